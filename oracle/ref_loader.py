@@ -1,0 +1,61 @@
+"""Load the UNMODIFIED reference (/root/reference) in the build container.
+
+TEST INFRASTRUCTURE ONLY -- used by oracle/make_golden.py and oracle/check_oracle_vs_ref.py to
+produce / validate fixtures.  Nothing on the product path imports this, and nothing that runs
+on the GPU box may (the reference does not exist there).
+
+Two shims:
+ 1. oracle/ref_shim/ supplies stand-ins for `gym`, `matplotlib`, `mpl_toolkits` (absent here).
+ 2. ctr_reach_envs/envs/model.py:107 builds a ragged nested list which numpy >= 1.24 rejects;
+    an import hook substitutes `uy[0]`/`ux[0]` -> `uy[0, 0]`/`ux[0, 0]` at load time (same
+    arithmetic, the reference file on disk stays the source of truth).
+"""
+import importlib.abc
+import importlib.machinery
+import os
+import sys
+
+REF_ROOT = os.environ.get('CTR_REFERENCE_ROOT', '/root/reference')
+_SHIM = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'ref_shim')
+
+
+class _PatchedLoader(importlib.machinery.SourceFileLoader):
+    def get_data(self, path):
+        data = super().get_data(path)
+        if path.endswith(os.path.join('envs', 'model.py')):
+            src = data.decode()
+            old = "u_hat = np.array([(0, - uz[0], uy[0]), (uz[0], 0, -ux[0]), (-uy[0], ux[0], 0)])"
+            new = "u_hat = np.array([(0, - uz[0], uy[0, 0]), (uz[0], 0, -ux[0, 0]), (-uy[0, 0], ux[0, 0], 0)])"
+            assert old in src, "reference model.py:107 changed; update the loader patch"
+            data = src.replace(old, new).encode()
+        return data
+
+    def source_to_code(self, data, path, *, _optimize=-1):
+        return super().source_to_code(data, path, _optimize=_optimize)
+
+
+class _Finder(importlib.abc.MetaPathFinder):
+    def find_spec(self, fullname, path, target=None):
+        if fullname != 'ctr_reach_envs.envs.model':
+            return None
+        fn = os.path.join(REF_ROOT, 'ctr_reach_envs', 'envs', 'model.py')
+        return importlib.machinery.ModuleSpec(fullname, _PatchedLoader(fullname, fn), origin=fn)
+
+
+def available():
+    return os.path.isfile(os.path.join(REF_ROOT, 'ctr_reach_envs', 'envs', 'model.py'))
+
+
+def load():
+    """Import and return the reference package `ctr_reach_envs` (and the gym shim)."""
+    if 'ctr_reach_envs' in sys.modules and not getattr(sys.modules['ctr_reach_envs'], '__file__', '').startswith(REF_ROOT):
+        raise RuntimeError("a different `ctr_reach_envs` is already imported; run the reference in its own process")
+    sys.dont_write_bytecode = True  # /root/reference is read-only
+    for p in (REF_ROOT, _SHIM):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    if not any(isinstance(f, _Finder) for f in sys.meta_path):
+        sys.meta_path.insert(0, _Finder())
+    import ctr_reach_envs  # noqa
+    import gym  # noqa
+    return ctr_reach_envs, gym
