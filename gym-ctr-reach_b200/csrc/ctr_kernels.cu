@@ -1,0 +1,976 @@
+// ctr_kernels.cu -- kernels and C-ABI (include/ctr_b200.h) of libctr_b200.so.  sm_100a only; no CPU fallback.
+//
+// Kernels (all: 3 lanes per environment, 10 environments per warp, see ctr_device.cuh):
+//   k_fk      joints -> tip / R / info                     (Model.forward_kinematics, model.py:30-70)
+//   k_step    10 x set_action -> FK -> reward/done/success/error -> observation -> stats, appends finished
+//             envs to the reset list                       (CtrReachEnv.step, ctr_reach_env.py:124-158)
+//   k_reset   goal / start sampling (Philox) -> 2 FK -> observation   (CtrReachEnv.reset, ctr_reach_env.py:70-114)
+//   k_reward / k_relabel   HER compute_reward              (ctr_reach_env.py:160-170)
+//   k_set_action           standalone constraint op        (Obs.set_action, obs.py:166-183)
+//   k_mask_to_list         compaction of an explicit reset mask
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/ctr_b200.h"
+#include "ctr_device.cuh"
+
+using namespace ctr;
+
+namespace {
+
+thread_local std::string g_err;
+
+#define CTR_FAIL(msg)                                                           \
+    do {                                                                        \
+        g_err = std::string(__func__) + ": " + (msg);                           \
+        return 1;                                                               \
+    } while (0)
+#define CTR_CUDA(call)                                                          \
+    do {                                                                        \
+        cudaError_t e__ = (call);                                               \
+        if (e__ != cudaSuccess) {                                               \
+            g_err = std::string(__func__) + ": " #call ": " + cudaGetErrorString(e__); \
+            return 2;                                                           \
+        }                                                                       \
+    } while (0)
+
+constexpr int BLOCK = 128;                       // 4 warps = 40 environments per block
+constexpr int ENVS_PER_BLOCK = (BLOCK / 32) * ENVS_PER_WARP;
+constexpr int N_STATS = 16;
+enum { ST_EPISODES = 0, ST_SUCCESSES, ST_SUM_ERROR, ST_SUM_RETURN, ST_SUM_LENGTH, ST_STEPS, ST_RESETS, ST_DRAWS,
+       ST_FK_FAILED, ST_GOAL_STUCK, ST_NFEV, ST_ATTEMPTS, ST_SECTIONS, ST_FK_COUNT };
+
+struct DevPtrs {
+    float* joints;
+    double* desired_goal;
+    float* desired_joints;
+    float* starting_joints;
+    double* starting_position;
+    double* achieved;
+    double* orientation;
+    int32_t* t;
+    int32_t* system;
+    uint32_t* episode;
+    double* obs;
+    double* reward;
+    uint8_t* done;
+    uint8_t* success;
+    double* error;
+    double* terminal_obs;
+    double* terminal_achieved;
+    double* tube_params;   // may be null
+    int32_t* nfev;
+    double* stats;
+    int32_t* reset_list;
+    int32_t* reset_count;
+};
+
+struct KArgs {
+    DevPtrs p;
+    const SysConst* sys;
+    const double* raw_tubes;   // [n_systems][3][8] nominal tube table (domain randomisation)
+    int64_t n;
+    int32_t n_systems, n_substeps, max_steps, rep, reward_mode, auto_reset, resample_joints, rk4_steps, obs_dim;
+    int32_t use_params;        // tube_params holds valid per-env constants
+    double tol, rtol, atol, domain_rand;
+    uint2 key;
+    int64_t env_offset;
+    int64_t act_stride_field, act_stride_env;   // action element (i, env) at action[i * stride_field + env * stride_env]
+};
+
+__device__ __forceinline__ void stage_sys(SysConst* s_sys, const SysConst* sys, int n_systems) {
+    const int words = n_systems * (int)(sizeof(SysConst) / 4);
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(sys);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(s_sys);
+    for (int i = threadIdx.x; i < words; i += blockDim.x) dst[i] = src[i];
+    __syncthreads();
+}
+
+__device__ __forceinline__ void load_consts(const SysConst& sc, const double* params, int64_t n, int64_t env,
+                                            bool use_params, double (&C)[18]) {
+    if (use_params) {
+#pragma unroll
+        for (int i = 0; i < 18; ++i) C[i] = __ldg(params + (int64_t)i * n + env);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            C[i] = sc.L[i];
+            C[3 + i] = sc.Lc[i];
+            C[6 + i] = sc.EI[i];
+            C[9 + i] = sc.GJ[i];
+            C[12 + i] = sc.Ux[i];
+            C[15 + i] = sc.Uy[i];
+        }
+    }
+}
+
+// warp-level sum of a per-environment quantity (counted once per group: only lane j == 0 contributes)
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    return v;
+}
+
+// observation of one env written cooperatively by its 3 lanes (obs.py:136-164, obs_utils.py:41-53,69-80).
+// proprioceptive: trig of the float32 joints in float32.  egocentric: prop2ego's np.diff(..., prepend=0) promotes the
+// float32 joints to float64, so the first differences and the trig are float64 arithmetic.
+__device__ __forceinline__ void write_obs(double* obs, int64_t n, int64_t env, int j, const float (&q)[6], int rep,
+                                          double des_j, double ach_j, double tol, int system, int obs_dim) {
+    const float bf = pick3(j, q[0], q[1], q[2]), af = pick3(j, q[3], q[4], q[5]);
+    double b, c, s;
+    if (rep == CTR_REP_EGOCENTRIC) {
+        b = __dsub_rn((double)bf, (double)pick3(j, 0.f, q[0], q[1]));
+        const double a = __dsub_rn((double)af, (double)pick3(j, 0.f, q[3], q[4]));
+        sincos(a, &s, &c);
+    } else {
+        float sf, cf;
+        sincosf(af, &sf, &cf);
+        b = (double)bf;
+        c = (double)cf;
+        s = (double)sf;
+    }
+    obs[(int64_t)(3 * j + 0) * n + env] = c;
+    obs[(int64_t)(3 * j + 1) * n + env] = s;
+    obs[(int64_t)(3 * j + 2) * n + env] = b;
+    obs[(int64_t)(9 + j) * n + env] = __dsub_rn(des_j, ach_j);
+    if (j == 0) obs[(int64_t)12 * n + env] = tol;
+    if (j == 1 && obs_dim > 13) obs[(int64_t)13 * n + env] = (double)system;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+template <typename T, int INTEG>
+__global__ void __launch_bounds__(BLOCK) k_fk(const SysConst* __restrict__ sys, int n_systems,
+                                              const double* __restrict__ joints, const int32_t* __restrict__ system,
+                                              const double* __restrict__ params, int64_t n, double rtol, double atol,
+                                              int rk4_steps, double* __restrict__ tip, double* __restrict__ R,
+                                              int32_t* __restrict__ info_out, double* __restrict__ stats) {
+    __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
+    stage_sys(s_sys, sys, n_systems);
+    const LaneId id = lane_id();
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t env = warp * ENVS_PER_WARP + id.g;
+    const bool valid = (id.g < ENVS_PER_WARP) && (env < n);
+    const int64_t e = valid ? env : 0;
+    int sysid = system ? system[e] : 0;
+    sysid = min(max(sysid, 0), n_systems - 1);
+    double C[18];
+    load_consts(s_sys[sysid], params, n, e, params != nullptr, C);
+    double beta[3], alpha[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        beta[i] = joints[(int64_t)i * n + e];
+        alpha[i] = joints[(int64_t)(3 + i) * n + e];
+    }
+    T y[6];
+    FkInfo info;
+    fk_group<T, INTEG>(id, valid, C, C + 3, C + 6, C + 9, C + 12, C + 15, beta, alpha, rtol, atol, rk4_steps, y, info);
+    if (valid) {
+        tip[(int64_t)id.j * n + env] = (double)y[2];
+        if (R) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) R[(int64_t)(3 * id.j + c) * n + env] = (double)y[3 + c];
+        }
+        if (info_out && id.j == 0) {
+            info_out[env] = info.nfev;
+            info_out[n + env] = info.nacc;
+            info_out[2 * n + env] = info.nrej;
+            info_out[3 * n + env] = info.nsec;
+        }
+        if (info.failed && id.j == 0 && stats) atomicAdd(stats + ST_FK_FAILED, 1.0);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+template <typename T, int INTEG>
+__global__ void __launch_bounds__(BLOCK) k_step(const KArgs a, const float* __restrict__ action) {
+    __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
+    stage_sys(s_sys, a.sys, a.n_systems);
+    const LaneId id = lane_id();
+    const int64_t n = a.n;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t env = warp * ENVS_PER_WARP + id.g;
+    const bool valid = (id.g < ENVS_PER_WARP) && (env < n);
+    const int64_t e = valid ? env : 0;
+    const int j = id.j;
+    const DevPtrs& p = a.p;
+
+    const int sysid = p.system[e];
+    const SysConst& sc = s_sys[sysid];
+    float q[6], act[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        q[i] = p.joints[(int64_t)i * n + e];
+        act[i] = action[(int64_t)i * a.act_stride_field + e * a.act_stride_env];
+    }
+    set_action(q, act, sc, a.n_substeps);                                  // ctr_reach_env.py:134-135
+
+    double C[18];
+    load_consts(sc, p.tube_params, n, e, a.use_params != 0, C);
+    double beta[3] = {(double)q[0], (double)q[1], (double)q[2]};           // model.py:50-51
+    double alpha[3] = {(double)q[3], (double)q[4], (double)q[5]};
+    T y[6];
+    FkInfo info;
+    fk_group<T, INTEG>(id, valid, C, C + 3, C + 6, C + 9, C + 12, C + 15, beta, alpha, a.rtol, a.atol, a.rk4_steps, y, info);
+
+    // ---- reward / done / success / error (ctr_reach_env.py:138-140, 155-156, 168-170)
+    const double ach_j = (double)y[2];
+    const double des_j = p.desired_goal[(int64_t)j * n + e];
+    const double diff = __dsub_rn(ach_j, des_j);
+    const double sq = __dmul_rn(diff, diff);
+    const double s0 = __shfl_sync(FULL, sq, id.l0), s1 = __shfl_sync(FULL, sq, id.l0 + 1), s2 = __shfl_sync(FULL, sq, id.l0 + 2);
+    const double dist = __dsqrt_rn(__dadd_rn(__dadd_rn(s0, s1), s2));
+    const int t_new = p.t[e] + 1;
+    const bool far = dist > a.tol;
+    const double reward = (a.reward_mode == CTR_REWARD_DENSE) ? -dist : (far ? -1.0 : -0.0);
+    const bool done = (!far) || (t_new >= a.max_steps);
+    const bool success = dist < a.tol;
+
+    if (valid) {
+        p.joints[(int64_t)j * n + env] = pick3(j, q[0], q[1], q[2]);
+        p.joints[(int64_t)(3 + j) * n + env] = pick3(j, q[3], q[4], q[5]);
+        p.achieved[(int64_t)j * n + env] = ach_j;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) p.orientation[(int64_t)(3 * j + c) * n + env] = (double)y[3 + c];
+        write_obs(p.obs, n, env, j, q, a.rep, des_j, ach_j, a.tol, sysid, a.obs_dim);
+        if (done && a.auto_reset) {
+            write_obs(p.terminal_obs, n, env, j, q, a.rep, des_j, ach_j, a.tol, sysid, a.obs_dim);
+            p.terminal_achieved[(int64_t)j * n + env] = ach_j;
+        }
+        if (j == 0) {
+            p.reward[env] = reward;
+            p.done[env] = done ? 1 : 0;
+            p.success[env] = success ? 1 : 0;
+            p.error[env] = dist;
+            p.t[env] = t_new;
+            p.nfev[env] = info.nfev;
+            if (done && a.auto_reset) {
+                int slot = atomicAdd(p.reset_count, 1);
+                p.reset_list[slot] = (int32_t)env;
+            }
+        }
+    }
+    // ---- episode statistics: one atomic per warp per counter
+    const bool lead = valid && j == 0;
+    double v_ep = (lead && done) ? 1.0 : 0.0;
+    double v_su = (lead && done && success) ? 1.0 : 0.0;
+    double v_er = (lead && done) ? dist : 0.0;
+    double v_rt = lead ? reward : 0.0;
+    double v_ln = (lead && done) ? (double)t_new : 0.0;
+    double v_st = lead ? 1.0 : 0.0;
+    double v_fl = (lead && info.failed) ? 1.0 : 0.0;
+    double v_nf = lead ? (double)info.nfev : 0.0;
+    double v_at = lead ? (double)(info.nacc + info.nrej) : 0.0;
+    double v_sc = lead ? (double)info.nsec : 0.0;
+    v_nf = warp_sum(v_nf); v_at = warp_sum(v_at); v_sc = warp_sum(v_sc);
+    v_ep = warp_sum(v_ep); v_su = warp_sum(v_su); v_er = warp_sum(v_er); v_rt = warp_sum(v_rt);
+    v_ln = warp_sum(v_ln); v_st = warp_sum(v_st); v_fl = warp_sum(v_fl);
+    if (id.lane == 0) {
+        if (v_ep != 0.0) {
+            atomicAdd(p.stats + ST_EPISODES, v_ep);
+            atomicAdd(p.stats + ST_SUM_ERROR, v_er);
+            atomicAdd(p.stats + ST_SUM_LENGTH, v_ln);
+            if (v_su != 0.0) atomicAdd(p.stats + ST_SUCCESSES, v_su);
+        }
+        atomicAdd(p.stats + ST_SUM_RETURN, v_rt);
+        atomicAdd(p.stats + ST_STEPS, v_st);
+        atomicAdd(p.stats + ST_NFEV, v_nf);
+        atomicAdd(p.stats + ST_ATTEMPTS, v_at);
+        atomicAdd(p.stats + ST_SECTIONS, v_sc);
+        atomicAdd(p.stats + ST_FK_COUNT, v_st);
+        if (v_fl != 0.0) atomicAdd(p.stats + ST_FK_FAILED, v_fl);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// reset: a warp serves 5 environments; even groups compute the desired goal, odd groups the starting position.
+template <typename T, int INTEG>
+__global__ void __launch_bounds__(BLOCK) k_reset(const KArgs a, const int32_t* __restrict__ list,
+                                                 const int32_t* __restrict__ count_ptr, const double* __restrict__ goal,
+                                                 const int32_t* __restrict__ system_in) {
+    __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
+    stage_sys(s_sys, a.sys, a.n_systems);
+    const LaneId id = lane_id();
+    const int64_t n = a.n;
+    const int64_t count = count_ptr ? (int64_t)*count_ptr : n;
+    const int64_t warps_total = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const DevPtrs& p = a.p;
+    const int j = id.j;
+    const int which = id.g & 1;        // 0: desired goal, 1: starting position
+    for (int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; warp * 5 < count; warp += warps_total) {
+        const int64_t item = warp * 5 + (id.g >> 1);
+        const bool valid = (id.g < ENVS_PER_WARP) && (item < count);
+        const int64_t env = valid ? (list ? (int64_t)list[item] : item) : 0;
+        const uint64_t genv = (uint64_t)(a.env_offset + env);
+        const unsigned env_lo = (unsigned)genv, env_hi = (unsigned)(genv >> 32);
+        const unsigned episode = p.episode[env] + 1u;
+
+        int sysid;
+        if (system_in) sysid = min(max(system_in[env], 0), a.n_systems - 1);
+        else if (a.n_systems > 1) {                                      // ctr_reach_env.py:95 randint(n_systems)
+            uint4 r = philox4x32(make_uint4(env_lo, env_hi, episode, 2u << 16), a.key);
+            sysid = (int)(((uint64_t)r.x * (uint64_t)a.n_systems) >> 32);
+        } else sysid = 0;
+        const SysConst& sc = s_sys[sysid];
+
+        double C[18];
+        if (a.domain_rand > 0.0) {
+            // Model.randomize_parameters (model.py:20-28, model_utils.py:5-35): U(v - v r, v + v r) on d_i, d_o, E, G, Ux
+            const double* nom = a.raw_tubes + (int64_t)sysid * 24;
+#pragma unroll
+            for (int tb = 0; tb < 3; ++tb) {
+                uint4 r1 = philox4x32(make_uint4(env_lo, env_hi, episode, (3u << 16) | (unsigned)(2 * tb)), a.key);
+                uint4 r2 = philox4x32(make_uint4(env_lo, env_hi, episode, (3u << 16) | (unsigned)(2 * tb + 1)), a.key);
+                const double rr = a.domain_rand;
+                auto rnd = [rr](double v, unsigned bits) { return (v - v * rr) + ((v + v * rr) - (v - v * rr)) * u01(bits); };
+                double di = rnd(nom[tb * 8 + 2], r1.x), d_o = rnd(nom[tb * 8 + 3], r1.y);
+                double E = rnd(nom[tb * 8 + 4], r1.z), Gm = rnd(nom[tb * 8 + 5], r1.w), ux = rnd(nom[tb * 8 + 6], r2.x);
+                double do2 = d_o * d_o, di2 = di * di;
+                double d4 = do2 * do2 - di2 * di2;
+                C[tb] = nom[tb * 8 + 0];
+                C[3 + tb] = nom[tb * 8 + 1];
+                C[6 + tb] = E * ((3.141592653589793 * d4) / 64);           // Tube.py:15
+                C[9 + tb] = Gm * ((3.141592653589793 * d4) / 32);          // Tube.py:14
+                C[12 + tb] = ux;
+                C[15 + tb] = nom[tb * 8 + 7];
+            }
+        } else {
+            load_consts(sc, p.tube_params, n, env, a.use_params != 0, C);
+        }
+
+        float q[6];
+        bool do_fk = valid;
+        int tries = 0;
+        bool ok = true;
+        if (which == 0) {
+            if (goal) do_fk = false;                                     // ctr_reach_env.py:102-103
+            else tries = sample_goal(sc, a.key, env_lo, env_hi, episode, 0u, q, ok);   // :100
+        } else {
+            if (a.resample_joints) tries = sample_goal(sc, a.key, env_lo, env_hi, episode, 1u, q, ok);   // :106
+            else {
+#pragma unroll
+                for (int i = 0; i < 6; ++i) q[i] = p.joints[(int64_t)i * n + env];                      // :111
+            }
+        }
+        if (!do_fk) {
+#pragma unroll
+            for (int i = 0; i < 6; ++i) q[i] = 0.f;
+        }
+        double beta[3] = {(double)q[0], (double)q[1], (double)q[2]};
+        double alpha[3] = {(double)q[3], (double)q[4], (double)q[5]};
+        T y[6];
+        FkInfo info;
+        fk_group<T, INTEG>(id, do_fk, C, C + 3, C + 6, C + 9, C + 12, C + 15, beta, alpha, a.rtol, a.atol, a.rk4_steps, y, info);
+        double tip_j = (double)y[2];
+        if (which == 0 && goal) tip_j = goal[(int64_t)j * n + env];
+        const double des_j = __shfl_sync(FULL, tip_j, (id.lane + 32 - 3) & 31);   // the pair's desired-goal group
+        const double tol = a.tol;
+        if (valid) {
+            if (which == 0) {
+                p.desired_goal[(int64_t)j * n + env] = tip_j;
+                if (!goal) {
+                    p.desired_joints[(int64_t)j * n + env] = pick3(j, q[0], q[1], q[2]);
+                    p.desired_joints[(int64_t)(3 + j) * n + env] = pick3(j, q[3], q[4], q[5]);
+                }
+            } else {
+                const float bj = pick3(j, q[0], q[1], q[2]), aj = pick3(j, q[3], q[4], q[5]);
+                p.joints[(int64_t)j * n + env] = bj;
+                p.joints[(int64_t)(3 + j) * n + env] = aj;
+                p.starting_joints[(int64_t)j * n + env] = bj;
+                p.starting_joints[(int64_t)(3 + j) * n + env] = aj;
+                p.starting_position[(int64_t)j * n + env] = tip_j;
+                p.achieved[(int64_t)j * n + env] = tip_j;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) p.orientation[(int64_t)(3 * j + c) * n + env] = (double)y[3 + c];
+                write_obs(p.obs, n, env, j, q, a.rep, des_j, tip_j, tol, sysid, a.obs_dim);   // :114
+                if (a.domain_rand > 0.0 && p.tube_params) {
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) p.tube_params[(int64_t)(3 * i + j) * n + env] = C[3 * i + j];
+                }
+                if (j == 0) {
+                    p.t[env] = 0;                                                             // :78
+                    p.system[env] = sysid;
+                    p.episode[env] = episode;
+                    p.nfev[env] = info.nfev;
+                }
+            }
+            if (j == 0) {
+                if (which == 1) atomicAdd(p.stats + ST_RESETS, 1.0);
+                if (tries) atomicAdd(p.stats + ST_DRAWS, (double)tries);
+                if (info.failed) atomicAdd(p.stats + ST_FK_FAILED, 1.0);
+                if (!ok) atomicAdd(p.stats + ST_GOAL_STUCK, 1.0);                             // obs.py:204-205
+                if (do_fk) {
+                    atomicAdd(p.stats + ST_NFEV, (double)info.nfev);
+                    atomicAdd(p.stats + ST_ATTEMPTS, (double)(info.nacc + info.nrej));
+                    atomicAdd(p.stats + ST_SECTIONS, (double)info.nsec);
+                    atomicAdd(p.stats + ST_FK_COUNT, 1.0);
+                }
+            }
+        }
+    }
+}
+
+__global__ void k_mask_to_list(const uint8_t* __restrict__ mask, int64_t n, int32_t* __restrict__ list,
+                               int32_t* __restrict__ count) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && mask[i]) list[atomicAdd(count, 1)] = (int32_t)i;
+}
+
+__global__ void k_set_action(const SysConst* __restrict__ sys, int n_systems, float* __restrict__ joints,
+                             const float* __restrict__ action, const int32_t* __restrict__ system, int64_t n,
+                             int n_substeps) {
+    __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
+    stage_sys(s_sys, sys, n_systems);
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int s = system ? min(max(system[i], 0), n_systems - 1) : 0;
+    float q[6], a[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        q[k] = joints[(int64_t)k * n + i];
+        a[k] = action[(int64_t)k * n + i];
+    }
+    set_action(q, a, s_sys[s], n_substeps);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) joints[(int64_t)k * n + i] = q[k];
+}
+
+// compute_reward (ctr_reach_env.py:160-170): streaming, 56 B per transition (+24 when the obs error is rewritten)
+__global__ void k_reward(const double* __restrict__ ach, const double* __restrict__ des, int64_t m, double tol, int mode,
+                         double* __restrict__ reward, double* __restrict__ obs) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride) {
+        double a0 = ach[i], a1 = ach[m + i], a2 = ach[2 * m + i];
+        double d0 = des[i], d1 = des[m + i], d2 = des[2 * m + i];
+        double x = __dsub_rn(a0, d0), y = __dsub_rn(a1, d1), z = __dsub_rn(a2, d2);
+        double dist = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)), __dmul_rn(z, z)));
+        reward[i] = (mode == CTR_REWARD_DENSE) ? -dist : ((dist > tol) ? -1.0 : -0.0);
+        if (obs) {
+            obs[9 * m + i] = __dsub_rn(d0, a0);
+            obs[10 * m + i] = __dsub_rn(d1, a1);
+            obs[11 * m + i] = __dsub_rn(d2, a2);
+        }
+    }
+}
+
+// register-resident FMA chains: the measured FP64 / FP32 FMA-pipe peak that bounds this path (no such figure in
+// MEASURED_PEAKS.json)
+template <typename T>
+__global__ void __launch_bounds__(256) k_fma_peak(T* out, int iters, T b, T c) {
+    T a[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = (T)(threadIdx.x + k) * (T)1e-3;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = a[k] * b + c;
+    }
+    T s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += a[k];
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+}  // namespace
+
+// ================================================================================================================
+struct ctr_handle {
+    ctr_config cfg;
+    int64_t n;
+    int32_t device;
+    int32_t obs_dim;
+    double tol;
+    DevPtrs p;
+    SysConst* sys_dev;
+    double* raw_dev;
+    std::vector<SysConst> sys_host;
+    void* fields[CTR_F_COUNT];
+    int64_t field_bytes[CTR_F_COUNT];
+    std::vector<void*> allocs;
+    cudaStream_t stream;       // used by the *_host entry points
+    int use_params;
+    int64_t launches;
+    int sm_count;
+    // lazily allocated staging for host calls
+    float* stage_action;
+    double* stage_fk_in;
+    int64_t stage_fk_cap;
+    void* stage_fk_dev;
+};
+
+namespace {
+
+void derive_system(const double tube[3][8], int constrain_alpha, SysConst& sc) {
+    const float PI_F = 3.14159274101257324f;
+    for (int i = 0; i < 3; ++i) {
+        const double* t = tube[i];
+        const double di = t[2], d_o = t[3];
+        const double J = (M_PI * (pow(d_o, 4) - pow(di, 4))) / 32;   // Tube.py:14
+        const double I = (M_PI * (pow(d_o, 4) - pow(di, 4))) / 64;   // Tube.py:15
+        sc.L[i] = t[0];
+        sc.Lc[i] = t[1];
+        sc.EI[i] = t[4] * I;                                         // Segment.py:57
+        sc.GJ[i] = t[5] * J;                                         // Segment.py:59
+        sc.Ux[i] = t[6];
+        sc.Uy[i] = t[7];
+        sc.low[i] = (float)(-t[0] + 1e-3);                           // obs.py:14,59: -L + EXT_TOL as float32
+        sc.high[i] = 0.f;
+        sc.low[3 + i] = constrain_alpha ? -PI_F : -INFINITY;         // obs.py:64-75
+        sc.high[3 + i] = constrain_alpha ? PI_F : INFINITY;
+        sc.Lf[i] = (float)t[0];
+        sc.slow[i] = sc.low[i];
+    }
+    sc.d10 = (float)(tube[1][0] - tube[0][0]);                       // obs.py:181 (python-float difference -> float32)
+    sc.d21 = (float)(tube[2][0] - tube[1][0]);
+}
+
+template <typename Tp>
+int dev_alloc(ctr_handle* h, Tp** out, int64_t count) {
+    void* ptr = nullptr;
+    size_t bytes = (size_t)(count > 0 ? count : 1) * sizeof(Tp);
+    CTR_CUDA(cudaMalloc(&ptr, bytes));
+    CTR_CUDA(cudaMemset(ptr, 0, bytes));
+    h->allocs.push_back(ptr);
+    *out = (Tp*)ptr;
+    return 0;
+}
+
+KArgs make_args(const ctr_handle* h) {
+    KArgs a;
+    a.p = h->p;
+    a.sys = h->sys_dev;
+    a.raw_tubes = h->raw_dev;
+    a.n = h->n;
+    a.n_systems = h->cfg.n_systems;
+    a.n_substeps = h->cfg.n_substeps;
+    a.max_steps = h->cfg.max_steps_per_episode;
+    a.rep = h->cfg.joint_representation;
+    a.reward_mode = h->cfg.reward_mode;
+    a.auto_reset = h->cfg.auto_reset;
+    a.resample_joints = h->cfg.resample_joints;
+    a.rk4_steps = h->cfg.rk4_steps;
+    a.obs_dim = h->obs_dim;
+    a.use_params = h->use_params;
+    a.tol = h->tol;
+    a.rtol = h->cfg.rtol;
+    a.atol = h->cfg.atol;
+    a.domain_rand = h->cfg.domain_rand;
+    a.key = make_uint2((unsigned)h->cfg.seed, (unsigned)(h->cfg.seed >> 32));
+    a.env_offset = h->cfg.env_offset;
+    a.act_stride_field = h->n;
+    a.act_stride_env = 1;
+    return a;
+}
+
+inline int grid_for(int64_t n_envs) { return (int)((n_envs + ENVS_PER_BLOCK - 1) / ENVS_PER_BLOCK); }
+
+#define DISPATCH(KERNEL, integ, prec, ...)                                           \
+    do {                                                                             \
+        if ((prec) == CTR_PRECISION_F64) {                                           \
+            if ((integ) == CTR_INTEGRATOR_DP45) KERNEL<double, 0> __VA_ARGS__;       \
+            else KERNEL<double, 1> __VA_ARGS__;                                      \
+        } else {                                                                     \
+            if ((integ) == CTR_INTEGRATOR_DP45) KERNEL<float, 0> __VA_ARGS__;        \
+            else KERNEL<float, 1> __VA_ARGS__;                                       \
+        }                                                                            \
+    } while (0)
+
+int launch_reset(ctr_handle* h, const int32_t* list, const int32_t* count_ptr, int64_t max_items, const double* goal,
+                 const int32_t* system, cudaStream_t st) {
+    if (max_items <= 0) return 0;
+    KArgs a = make_args(h);
+    int64_t warps = (max_items + 4) / 5;
+    int64_t blocks = (warps + (BLOCK / 32) - 1) / (BLOCK / 32);
+    // when the item count lives on the device, cap the grid (grid-stride loop inside) so that the common case of
+    // few finished environments does not launch N/20 empty blocks
+    if (count_ptr) blocks = blocks < (int64_t)h->sm_count * 8 ? blocks : (int64_t)h->sm_count * 8;
+    DISPATCH(k_reset, h->cfg.integrator, h->cfg.precision, <<<(int)blocks, BLOCK, 0, st>>>(a, list, count_ptr, goal, system));
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* ctr_last_error(void) { return g_err.c_str(); }
+int ctr_abi_version(void) { return CTR_ABI_VERSION; }
+
+int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle** out) {
+    if (!cfg || !out) CTR_FAIL("null argument");
+    if (cfg->abi_version != CTR_ABI_VERSION) CTR_FAIL("ctr_config.abi_version mismatch");
+    if (n_envs < 1 || n_envs > 2000000000LL) CTR_FAIL("n_envs out of range");
+    if (cfg->n_systems < 1 || cfg->n_systems > CTR_MAX_SYSTEMS) CTR_FAIL("n_systems out of range");
+    if (cfg->joint_representation != CTR_REP_EGOCENTRIC && cfg->joint_representation != CTR_REP_PROPRIOCEPTIVE)
+        CTR_FAIL("Incorrect joint representation selected.");
+    if (cfg->integrator != CTR_INTEGRATOR_DP45 && cfg->integrator != CTR_INTEGRATOR_RK4) CTR_FAIL("unknown integrator");
+    if (cfg->precision != CTR_PRECISION_F64 && cfg->precision != CTR_PRECISION_F32) CTR_FAIL("unknown precision");
+    if (cfg->integrator == CTR_INTEGRATOR_RK4 && cfg->rk4_steps < 1) CTR_FAIL("rk4_steps must be >= 1");
+    if (cfg->n_substeps < 0 || cfg->max_steps_per_episode < 1) CTR_FAIL("bad n_substeps / max_steps_per_episode");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) CTR_FAIL("no CUDA device available (this library has no CPU fallback)");
+    if (device < 0 || device >= ndev) CTR_FAIL("device index out of range");
+    CTR_CUDA(cudaSetDevice(device));
+    ctr_handle* h = new ctr_handle();
+    h->cfg = *cfg;
+    h->n = n_envs;
+    h->device = device;
+    h->obs_dim = cfg->n_systems > 1 ? 14 : 13;
+    h->tol = cfg->initial_tol;
+    h->use_params = 0;
+    h->launches = 0;
+    h->stage_action = nullptr;
+    h->stage_fk_in = nullptr;
+    h->stage_fk_cap = 0;
+    h->stage_fk_dev = nullptr;
+    cudaDeviceProp prop;
+    CTR_CUDA(cudaGetDeviceProperties(&prop, device));
+    h->sm_count = prop.multiProcessorCount;
+    h->sys_host.resize(CTR_MAX_SYSTEMS);
+    memset(h->sys_host.data(), 0, sizeof(SysConst) * CTR_MAX_SYSTEMS);
+    for (int s = 0; s < cfg->n_systems; ++s) derive_system(cfg->tube[s], cfg->constrain_alpha, h->sys_host[s]);
+    const int64_t N = n_envs, D = h->obs_dim;
+    int rc = 0;
+    rc |= dev_alloc(h, &h->sys_dev, CTR_MAX_SYSTEMS);
+    rc |= dev_alloc(h, &h->raw_dev, CTR_MAX_SYSTEMS * 24);
+    rc |= dev_alloc(h, &h->p.joints, 6 * N);
+    rc |= dev_alloc(h, &h->p.desired_goal, 3 * N);
+    rc |= dev_alloc(h, &h->p.desired_joints, 6 * N);
+    rc |= dev_alloc(h, &h->p.starting_joints, 6 * N);
+    rc |= dev_alloc(h, &h->p.starting_position, 3 * N);
+    rc |= dev_alloc(h, &h->p.achieved, 3 * N);
+    rc |= dev_alloc(h, &h->p.orientation, 9 * N);
+    rc |= dev_alloc(h, &h->p.t, N);
+    rc |= dev_alloc(h, &h->p.system, N);
+    rc |= dev_alloc(h, &h->p.episode, N);
+    rc |= dev_alloc(h, &h->p.obs, D * N);
+    rc |= dev_alloc(h, &h->p.reward, N);
+    rc |= dev_alloc(h, &h->p.done, N);
+    rc |= dev_alloc(h, &h->p.success, N);
+    rc |= dev_alloc(h, &h->p.error, N);
+    rc |= dev_alloc(h, &h->p.terminal_obs, D * N);
+    rc |= dev_alloc(h, &h->p.terminal_achieved, 3 * N);
+    rc |= dev_alloc(h, &h->p.tube_params, 18 * N);
+    rc |= dev_alloc(h, &h->p.nfev, N);
+    rc |= dev_alloc(h, &h->p.stats, N_STATS);
+    rc |= dev_alloc(h, &h->p.reset_list, N);
+    rc |= dev_alloc(h, &h->p.reset_count, 1);
+    if (rc) {
+        std::string keep = g_err;
+        ctr_destroy(h);
+        g_err = keep;
+        return 2;
+    }
+    CTR_CUDA(cudaMemcpy(h->sys_dev, h->sys_host.data(), sizeof(SysConst) * CTR_MAX_SYSTEMS, cudaMemcpyHostToDevice));
+    CTR_CUDA(cudaMemcpy(h->raw_dev, cfg->tube, sizeof(double) * CTR_MAX_SYSTEMS * 24, cudaMemcpyHostToDevice));
+    CTR_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    void* f[CTR_F_COUNT] = {h->p.joints, h->p.desired_goal, h->p.desired_joints, h->p.starting_joints,
+                            h->p.starting_position, h->p.achieved, h->p.orientation, h->p.t, h->p.system, h->p.episode,
+                            h->p.obs, h->p.reward, h->p.done, h->p.success, h->p.error, h->p.terminal_obs,
+                            h->p.terminal_achieved, h->p.tube_params, h->p.nfev, h->p.stats};
+    int64_t b[CTR_F_COUNT] = {24 * N, 24 * N, 24 * N, 24 * N, 24 * N, 24 * N, 72 * N, 4 * N, 4 * N, 4 * N,
+                              8 * D * N, 8 * N, N, N, 8 * N, 8 * D * N, 24 * N, 144 * N, 4 * N, 8 * 8};
+    for (int i = 0; i < CTR_F_COUNT; ++i) {
+        h->fields[i] = f[i];
+        h->field_bytes[i] = b[i];
+    }
+    *out = h;
+    return 0;
+}
+
+int ctr_destroy(ctr_handle* h) {
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    for (void* ptr : h->allocs) cudaFree(ptr);
+    if (h->stage_action) cudaFreeHost(h->stage_action);
+    if (h->stage_fk_in) cudaFreeHost(h->stage_fk_in);
+    if (h->stage_fk_dev) cudaFree(h->stage_fk_dev);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return 0;
+}
+
+int64_t ctr_num_envs(const ctr_handle* h) { return h ? h->n : -1; }
+int32_t ctr_obs_dim(const ctr_handle* h) { return h ? h->obs_dim : -1; }
+int64_t ctr_launch_count(const ctr_handle* h) { return h ? h->launches : -1; }
+
+int ctr_buffer(ctr_handle* h, int32_t field, void** dev_ptr, int64_t* nbytes) {
+    if (!h || field < 0 || field >= CTR_F_COUNT) CTR_FAIL("bad handle / field");
+    if (dev_ptr) *dev_ptr = h->fields[field];
+    if (nbytes) *nbytes = h->field_bytes[field];
+    return 0;
+}
+
+int ctr_system_constants(const ctr_handle* h, int32_t system, double out18[CTR_ENV_PARAMS]) {
+    if (!h || system < 0 || system >= h->cfg.n_systems) CTR_FAIL("bad handle / system");
+    const SysConst& s = h->sys_host[system];
+    for (int i = 0; i < 3; ++i) {
+        out18[i] = s.L[i];
+        out18[3 + i] = s.Lc[i];
+        out18[6 + i] = s.EI[i];
+        out18[9 + i] = s.GJ[i];
+        out18[12 + i] = s.Ux[i];
+        out18[15 + i] = s.Uy[i];
+    }
+    return 0;
+}
+
+int ctr_set_tolerance(ctr_handle* h, double tol) {
+    if (!h) CTR_FAIL("null handle");
+    h->tol = tol;
+    return 0;
+}
+double ctr_get_tolerance(const ctr_handle* h) { return h ? h->tol : -1.0; }
+
+int ctr_seed(ctr_handle* h, uint64_t seed) {
+    if (!h) CTR_FAIL("null handle");
+    h->cfg.seed = seed;
+    return 0;
+}
+
+int ctr_set_tube_params(ctr_handle* h, const double* params_dev, void* stream) {
+    if (!h) CTR_FAIL("null handle");
+    CTR_CUDA(cudaSetDevice(h->device));
+    if (!params_dev) {
+        h->use_params = 0;
+        return 0;
+    }
+    CTR_CUDA(cudaMemcpyAsync(h->p.tube_params, params_dev, sizeof(double) * 18 * h->n, cudaMemcpyDeviceToDevice,
+                             (cudaStream_t)stream));
+    h->use_params = 1;
+    return 0;
+}
+
+int ctr_fk(ctr_handle* h, const double* joints_dev, const int32_t* system_dev, const double* params_dev, int64_t n,
+           int32_t integrator, int32_t precision, double* tip_dev, double* R_dev, int32_t* info_dev, void* stream) {
+    if (!h || !joints_dev || !tip_dev) CTR_FAIL("null argument");
+    if (n <= 0) return 0;
+    CTR_CUDA(cudaSetDevice(h->device));
+    if (integrator < 0) integrator = h->cfg.integrator;
+    if (precision < 0) precision = h->cfg.precision;
+    int rk4 = h->cfg.rk4_steps > 0 ? h->cfg.rk4_steps : 8;
+    cudaStream_t st = (cudaStream_t)stream;
+    DISPATCH(k_fk, integrator, precision,
+             <<<grid_for(n), BLOCK, 0, st>>>(h->sys_dev, h->cfg.n_systems, joints_dev, system_dev, params_dev, n,
+                                             h->cfg.rtol, h->cfg.atol, rk4, tip_dev, R_dev, info_dev, h->p.stats));
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int ctr_fk_host(ctr_handle* h, const double* joints_host, const int32_t* system_host, int64_t n, int32_t integrator,
+                int32_t precision, double* tip_host, double* R_host, int32_t* info_host) {
+    if (!h || !joints_host || !tip_host) CTR_FAIL("null argument");
+    if (n <= 0) return 0;
+    CTR_CUDA(cudaSetDevice(h->device));
+    // device scratch: joints 6n f64 | tip 3n f64 | R 9n f64 | system n i32 | info 4n i32
+    const size_t bytes = (size_t)n * (8 * 18 + 4 * 5);
+    if (h->stage_fk_cap < n) {
+        if (h->stage_fk_dev) CTR_CUDA(cudaFree(h->stage_fk_dev));
+        h->stage_fk_dev = nullptr;
+        CTR_CUDA(cudaMalloc(&h->stage_fk_dev, bytes));
+        h->stage_fk_cap = n;
+    }
+    double* dj = (double*)h->stage_fk_dev;
+    double* dt = dj + 6 * n;
+    double* dR = dt + 3 * n;
+    int32_t* ds = (int32_t*)(dR + 9 * n);
+    int32_t* di = ds + n;
+    cudaStream_t st = h->stream;
+    CTR_CUDA(cudaMemcpyAsync(dj, joints_host, sizeof(double) * 6 * n, cudaMemcpyHostToDevice, st));
+    if (system_host) CTR_CUDA(cudaMemcpyAsync(ds, system_host, sizeof(int32_t) * n, cudaMemcpyHostToDevice, st));
+    int rc = ctr_fk(h, dj, system_host ? ds : nullptr, nullptr, n, integrator, precision, dt, dR, di, st);
+    if (rc) return rc;
+    CTR_CUDA(cudaMemcpyAsync(tip_host, dt, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost, st));
+    if (R_host) CTR_CUDA(cudaMemcpyAsync(R_host, dR, sizeof(double) * 9 * n, cudaMemcpyDeviceToHost, st));
+    if (info_host) CTR_CUDA(cudaMemcpyAsync(info_host, di, sizeof(int32_t) * 4 * n, cudaMemcpyDeviceToHost, st));
+    CTR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int ctr_set_action(ctr_handle* h, float* joints_dev, const float* action_dev, const int32_t* system_dev, int64_t n,
+                   int32_t n_substeps, void* stream) {
+    if (!h || !joints_dev || !action_dev) CTR_FAIL("null argument");
+    if (n <= 0) return 0;
+    CTR_CUDA(cudaSetDevice(h->device));
+    k_set_action<<<(int)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(h->sys_dev, h->cfg.n_systems, joints_dev,
+                                                                          action_dev, system_dev, n, n_substeps);
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int ctr_set_state_host(ctr_handle* h, const float* joints, const double* desired_goal, const int32_t* system,
+                       const int32_t* t) {
+    if (!h) CTR_FAIL("null handle");
+    CTR_CUDA(cudaSetDevice(h->device));
+    CTR_CUDA(cudaDeviceSynchronize());
+    if (joints) CTR_CUDA(cudaMemcpy(h->p.joints, joints, sizeof(float) * 6 * h->n, cudaMemcpyHostToDevice));
+    if (desired_goal) CTR_CUDA(cudaMemcpy(h->p.desired_goal, desired_goal, sizeof(double) * 3 * h->n, cudaMemcpyHostToDevice));
+    if (system) CTR_CUDA(cudaMemcpy(h->p.system, system, sizeof(int32_t) * h->n, cudaMemcpyHostToDevice));
+    if (t) CTR_CUDA(cudaMemcpy(h->p.t, t, sizeof(int32_t) * h->n, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+int ctr_reset(ctr_handle* h, const uint8_t* mask_dev, const double* goal_dev, const int32_t* system_dev, void* stream) {
+    if (!h) CTR_FAIL("null handle");
+    CTR_CUDA(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (mask_dev) {
+        CTR_CUDA(cudaMemsetAsync(h->p.reset_count, 0, sizeof(int32_t), st));
+        k_mask_to_list<<<(int)((h->n + 255) / 256), 256, 0, st>>>(mask_dev, h->n, h->p.reset_list, h->p.reset_count);
+        h->launches += 1;
+        CTR_CUDA(cudaGetLastError());
+        return launch_reset(h, h->p.reset_list, h->p.reset_count, h->n, goal_dev, system_dev, st);
+    }
+    return launch_reset(h, nullptr, nullptr, h->n, goal_dev, system_dev, st);
+}
+
+int ctr_step(ctr_handle* h, const float* action_dev, void* stream) {
+    return ctr_step_strided(h, action_dev, h ? h->n : 0, 1, stream);
+}
+
+int ctr_step_strided(ctr_handle* h, const float* action_dev, int64_t stride_field, int64_t stride_env, void* stream) {
+    if (!h || !action_dev) CTR_FAIL("null argument");
+    CTR_CUDA(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    KArgs a = make_args(h);
+    a.act_stride_field = stride_field;
+    a.act_stride_env = stride_env;
+    if (h->cfg.auto_reset) CTR_CUDA(cudaMemsetAsync(h->p.reset_count, 0, sizeof(int32_t), st));
+    DISPATCH(k_step, h->cfg.integrator, h->cfg.precision, <<<grid_for(h->n), BLOCK, 0, st>>>(a, action_dev));
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    if (h->cfg.auto_reset) return launch_reset(h, h->p.reset_list, h->p.reset_count, h->n, nullptr, nullptr, st);
+    return 0;
+}
+
+static int copy_out(ctr_handle* h, cudaStream_t st, double* obs, double* ach, double* des, double* rew, uint8_t* done,
+                    uint8_t* succ, double* err) {
+    const int64_t N = h->n;
+    if (obs) CTR_CUDA(cudaMemcpyAsync(obs, h->p.obs, sizeof(double) * h->obs_dim * N, cudaMemcpyDeviceToHost, st));
+    if (ach) CTR_CUDA(cudaMemcpyAsync(ach, h->p.achieved, sizeof(double) * 3 * N, cudaMemcpyDeviceToHost, st));
+    if (des) CTR_CUDA(cudaMemcpyAsync(des, h->p.desired_goal, sizeof(double) * 3 * N, cudaMemcpyDeviceToHost, st));
+    if (rew) CTR_CUDA(cudaMemcpyAsync(rew, h->p.reward, sizeof(double) * N, cudaMemcpyDeviceToHost, st));
+    if (done) CTR_CUDA(cudaMemcpyAsync(done, h->p.done, N, cudaMemcpyDeviceToHost, st));
+    if (succ) CTR_CUDA(cudaMemcpyAsync(succ, h->p.success, N, cudaMemcpyDeviceToHost, st));
+    if (err) CTR_CUDA(cudaMemcpyAsync(err, h->p.error, sizeof(double) * N, cudaMemcpyDeviceToHost, st));
+    CTR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int ctr_step_host(ctr_handle* h, const float* action_host, double* obs_host, double* achieved_host, double* desired_host,
+                  double* reward_host, uint8_t* done_host, uint8_t* success_host, double* error_host) {
+    if (!h || !action_host) CTR_FAIL("null argument");
+    CTR_CUDA(cudaSetDevice(h->device));
+    if (!h->stage_action) CTR_CUDA(cudaMalloc((void**)&h->stage_action, sizeof(float) * 6 * h->n));
+    cudaStream_t st = h->stream;
+    CTR_CUDA(cudaMemcpyAsync(h->stage_action, action_host, sizeof(float) * 6 * h->n, cudaMemcpyHostToDevice, st));
+    int rc = ctr_step(h, h->stage_action, st);
+    if (rc) return rc;
+    return copy_out(h, st, obs_host, achieved_host, desired_host, reward_host, done_host, success_host, error_host);
+}
+
+int ctr_reset_host(ctr_handle* h, double* obs_host, double* achieved_host, double* desired_host) {
+    if (!h) CTR_FAIL("null handle");
+    int rc = ctr_reset(h, nullptr, nullptr, nullptr, h->stream);
+    if (rc) return rc;
+    return copy_out(h, h->stream, obs_host, achieved_host, desired_host, nullptr, nullptr, nullptr, nullptr);
+}
+
+int ctr_compute_reward(ctr_handle* h, const double* achieved_dev, const double* desired_dev, int64_t m, double tol,
+                       int32_t mode, double* reward_dev, void* stream) {
+    return ctr_relabel(h, achieved_dev, desired_dev, m, tol, mode, reward_dev, nullptr, stream);
+}
+
+int ctr_relabel(ctr_handle* h, const double* achieved_dev, const double* new_desired_dev, int64_t m, double tol,
+                int32_t mode, double* reward_dev, double* obs_dev, void* stream) {
+    if (!h || !achieved_dev || !new_desired_dev || !reward_dev) CTR_FAIL("null argument");
+    if (m <= 0) return 0;
+    CTR_CUDA(cudaSetDevice(h->device));
+    if (tol < 0) tol = h->tol;
+    if (mode < 0) mode = h->cfg.reward_mode;
+    int64_t blocks = (m + 255) / 256;
+    int64_t cap = (int64_t)h->sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    k_reward<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(achieved_dev, new_desired_dev, m, tol, mode, reward_dev, obs_dev);
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int ctr_stats(ctr_handle* h, double out8_host[8], void* stream) {
+    if (!h || !out8_host) CTR_FAIL("null argument");
+    CTR_CUDA(cudaSetDevice(h->device));
+    double tmp[N_STATS];
+    CTR_CUDA(cudaMemcpyAsync(tmp, h->p.stats, sizeof(tmp), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    CTR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    for (int i = 0; i < 8; ++i) out8_host[i] = tmp[i];
+    if (tmp[ST_FK_FAILED] != 0.0 || tmp[ST_GOAL_STUCK] != 0.0) {
+        char buf[160];
+        snprintf(buf, sizeof buf, "%g forward-kinematics solves failed (NaN / step too small, model.py:69), %g goal samplings stuck (obs.py:205)",
+                 tmp[ST_FK_FAILED], tmp[ST_GOAL_STUCK]);
+        g_err = buf;
+        return 3;
+    }
+    return 0;
+}
+
+int ctr_work_counters(ctr_handle* h, double out4_host[4], void* stream) {
+    if (!h || !out4_host) CTR_FAIL("null argument");
+    CTR_CUDA(cudaSetDevice(h->device));
+    double tmp[N_STATS];
+    CTR_CUDA(cudaMemcpyAsync(tmp, h->p.stats, sizeof(tmp), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    CTR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    out4_host[0] = tmp[ST_NFEV];
+    out4_host[1] = tmp[ST_ATTEMPTS];
+    out4_host[2] = tmp[ST_SECTIONS];
+    out4_host[3] = tmp[ST_FK_COUNT];
+    return 0;
+}
+
+int ctr_measure_fma_peak(int32_t device, int32_t precision, double* tflops_out) {
+    if (!tflops_out) CTR_FAIL("null argument");
+    CTR_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CTR_CUDA(cudaGetDeviceProperties(&prop, device));
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 14;
+    void* out = nullptr;
+    CTR_CUDA(cudaMalloc(&out, (size_t)blocks * threads * 8));
+    cudaEvent_t e0, e1;
+    CTR_CUDA(cudaEventCreate(&e0));
+    CTR_CUDA(cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; ++rep) {
+        CTR_CUDA(cudaEventRecord(e0, 0));
+        if (precision == CTR_PRECISION_F64) k_fma_peak<double><<<blocks, threads>>>((double*)out, iters, 0.999999, 1e-7);
+        else k_fma_peak<float><<<blocks, threads>>>((float*)out, iters, 0.999999f, 1e-7f);
+        CTR_CUDA(cudaEventRecord(e1, 0));
+        CTR_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        CTR_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep > 0 && ms < best) best = ms;
+    }
+    CTR_CUDA(cudaGetLastError());
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    *tflops_out = 2.0 * 8.0 * (double)iters * (double)blocks * threads / (best * 1e-3) / 1e12;
+    return 0;
+}
+
+int ctr_stats_reset(ctr_handle* h, void* stream) {
+    if (!h) CTR_FAIL("null handle");
+    CTR_CUDA(cudaSetDevice(h->device));
+    CTR_CUDA(cudaMemsetAsync(h->p.stats, 0, sizeof(double) * N_STATS, (cudaStream_t)stream));
+    return 0;
+}
+
+}  // extern "C"

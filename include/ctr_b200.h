@@ -1,0 +1,182 @@
+/* ctr_b200.h -- C ABI of libctr_b200.so: the B200-native batched CTR-Reach environment step.
+ *
+ * The reference (keshaviyengar/gym-ctr-reach) is pure Python and has no FFI layer; the boundary it
+ * exposes for this path is its gym API (ctr_reach_envs/envs/ctr_reach_env.py).  Each entry point below
+ * names the reference method it replaces (file:line relative to /root/reference/ctr_reach_envs/).
+ * INTEGRATION.md shows the ctypes binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *  - plain C types only; every function returns 0 on success, non-zero on error; ctr_last_error()
+ *    returns a thread-local message.  No exceptions cross the ABI.
+ *  - a handle is bound to ONE CUDA device and is not thread-safe; handles are independent.
+ *  - "dev" pointers are device pointers on the handle's device, "host" pointers are host memory
+ *    (pinned or pageable).  Batched arrays are SoA: [field][n] (field-major, n contiguous).
+ *  - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Device-pointer
+ *    calls are asynchronous on that stream; *_host calls synchronise before returning.
+ *  - there is NO CPU fallback: without a CUDA device ctr_create fails.
+ */
+#ifndef CTR_B200_H
+#define CTR_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CTR_ABI_VERSION 1
+#define CTR_MAX_SYSTEMS 8
+#define CTR_NUM_TUBES 3
+#define CTR_TUBE_FIELDS 8   /* length, length_curved, diameter_inner, diameter_outer, stiffness,
+                               torsional_stiffness, x_curvature, y_curvature  (Tube.py:7-8) */
+#define CTR_ENV_PARAMS 18   /* per-env derived constants: L[3], Lc[3], EI[3], GJ[3], Ux[3], Uy[3] */
+
+enum { CTR_REP_EGOCENTRIC = 0, CTR_REP_PROPRIOCEPTIVE = 1 };   /* obs.py:147-151 */
+enum { CTR_INTEGRATOR_DP45 = 0,   /* scipy RK45 restated: adaptive Dormand-Prince 5(4), the parity mode */
+       CTR_INTEGRATOR_RK4 = 1 };  /* fixed-step classical RK4, rk4_steps per section (throughput mode)   */
+enum { CTR_PRECISION_F64 = 0,     /* ODE state / RHS in float64 (reference arithmetic)                   */
+       CTR_PRECISION_F32 = 1 };   /* ODE state / RHS in float32; segmentation stays float64              */
+enum { CTR_REWARD_SPARSE = 0,     /* -(d > tol)  (ctr_reach_env.py:168-170)                              */
+       CTR_REWARD_DENSE = 1 };    /* -d          (extension; BASELINE.json config 2)                     */
+
+/* Mirrors the kwargs of CtrReachEnv.__init__ (ctr_reach_env.py:14-17) and register() (__init__.py:6-94). */
+typedef struct ctr_config {
+    int32_t abi_version;                 /* must be CTR_ABI_VERSION */
+    int32_t n_systems;                   /* number of selected tube systems, 1..CTR_MAX_SYSTEMS */
+    double tube[CTR_MAX_SYSTEMS][CTR_NUM_TUBES][CTR_TUBE_FIELDS];
+    int32_t n_substeps;                  /* 10  (__init__.py:75)  */
+    int32_t max_steps_per_episode;       /* 150 (__init__.py:74)  */
+    int32_t joint_representation;        /* CTR_REP_*             */
+    int32_t constrain_alpha;             /* clip alpha to +-pi (obs.py:64-69) */
+    double extension_action_limit;       /* 0.001 m  (__init__.py:72) */
+    double rotation_action_limit_deg;    /* 5 deg    (__init__.py:73) */
+    int32_t resample_joints;             /* reset re-samples the starting joints (ctr_reach_env.py:104-112) */
+    int32_t auto_reset;                  /* VecEnv semantics: finished envs are reset inside ctr_step */
+    int32_t integrator;                  /* CTR_INTEGRATOR_* */
+    int32_t precision;                   /* CTR_PRECISION_*  */
+    int32_t rk4_steps;                   /* steps per section for CTR_INTEGRATOR_RK4 */
+    int32_t reward_mode;                 /* CTR_REWARD_*     */
+    double rtol, atol;                   /* 1e-3, 1e-6: solve_ivp defaults (model.py:149-151 passes none) */
+    double initial_tol;                  /* goal tolerance until ctr_set_tolerance is called */
+    double domain_rand;                  /* +-fraction on d_i, d_o, E, G, Ux at every reset (model_utils.py:15-19) */
+    uint64_t seed;                       /* Philox key */
+    int64_t env_offset;                  /* global index of this handle's env 0 (multi-GPU shards) */
+} ctr_config;
+
+typedef struct ctr_handle ctr_handle;
+
+/* State / output buffers owned by the handle (device memory, SoA).  ctr_buffer() returns the pointer. */
+enum ctr_field {
+    CTR_F_JOINTS = 0,          /* f32 [6][N]  current joints b0,b1,b2,a0,a1,a2 (Obs.joints)                 */
+    CTR_F_DESIRED_GOAL,        /* f64 [3][N]  (env.desired_goal)                                            */
+    CTR_F_DESIRED_JOINTS,      /* f32 [6][N]  (env.desired_joints)                                          */
+    CTR_F_STARTING_JOINTS,     /* f32 [6][N]  (env.starting_joints)                                         */
+    CTR_F_STARTING_POSITION,   /* f64 [3][N]  (env.starting_position)                                       */
+    CTR_F_ACHIEVED_GOAL,       /* f64 [3][N]  tip position after the last step / reset                      */
+    CTR_F_ORIENTATION,         /* f64 [9][N]  tip rotation matrix, row-major (extension; model.py:162)      */
+    CTR_F_T,                   /* i32 [N]     steps in the current episode (env.t)                          */
+    CTR_F_SYSTEM,              /* i32 [N]     index into the selected systems (env.system)                  */
+    CTR_F_EPISODE,             /* u32 [N]     episode counter (RNG stream position)                         */
+    CTR_F_OBS,                 /* f64 [D][N]  'observation' (obs.py:136-164), D = ctr_obs_dim()             */
+    CTR_F_REWARD,              /* f64 [N]                                                                   */
+    CTR_F_DONE,                /* u8  [N]                                                                   */
+    CTR_F_SUCCESS,             /* u8  [N]     info['is_success']                                            */
+    CTR_F_ERROR,               /* f64 [N]     info['error']                                                 */
+    CTR_F_TERMINAL_OBS,        /* f64 [D][N]  observation of the finished episode (valid where done, auto_reset) */
+    CTR_F_TERMINAL_ACHIEVED,   /* f64 [3][N]  achieved goal of the finished episode (valid where done)      */
+    CTR_F_TUBE_PARAMS,         /* f64 [18][N] per-env derived constants (only after ctr_set_tube_params / domain_rand) */
+    CTR_F_NFEV,                /* i32 [N]     RHS evaluations of the last FK of each env                    */
+    CTR_F_STATS,               /* f64 [8]     see ctr_stats()                                               */
+    CTR_F_COUNT
+};
+
+const char *ctr_last_error(void);
+int ctr_abi_version(void);
+
+/* CtrReachEnv.__init__ (ctr_reach_env.py:14-68): build N environments on `device`. */
+int ctr_create(const ctr_config *cfg, int64_t n_envs, int32_t device, ctr_handle **out);
+int ctr_destroy(ctr_handle *h);
+int64_t ctr_num_envs(const ctr_handle *h);
+int32_t ctr_obs_dim(const ctr_handle *h);   /* 13, or 14 when n_systems > 1 (obs.py:153-156) */
+int ctr_buffer(ctr_handle *h, int32_t field, void **dev_ptr, int64_t *nbytes);
+
+/* Derived per-system constants L,Lc,EI,GJ,Ux,Uy (Tube.py:14-15, Segment.py:57-59) as the device uses them. */
+int ctr_system_constants(const ctr_handle *h, int32_t system, double out18[CTR_ENV_PARAMS]);
+
+/* GoalTolerance.get_tol()/update() (goal_tolerance.py:34-55): the schedule runs on the host, the value is set here. */
+int ctr_set_tolerance(ctr_handle *h, double tol);
+double ctr_get_tolerance(const ctr_handle *h);
+
+/* CtrReachEnv.seed (ctr_reach_env.py:116-122). */
+int ctr_seed(ctr_handle *h, uint64_t seed);
+
+/* Model.randomize_parameters (model.py:20-28): explicit per-env constants, f64 [18][N] on the device; NULL
+ * returns to the per-system constants. */
+int ctr_set_tube_params(ctr_handle *h, const double *params_dev, void *stream);
+
+/* Model.forward_kinematics (model.py:30-70).  joints f64 [6][n]; system i32 [n] or NULL (system 0);
+ * params f64 [18][n] or NULL; outputs: tip f64 [3][n], R f64 [9][n] or NULL, info i32 [4][n] or NULL
+ * (nfev, accepted steps, rejected steps, sections).  integrator/precision < 0 use the handle's config. */
+int ctr_fk(ctr_handle *h, const double *joints_dev, const int32_t *system_dev, const double *params_dev, int64_t n,
+           int32_t integrator, int32_t precision, double *tip_dev, double *R_dev, int32_t *info_dev, void *stream);
+int ctr_fk_host(ctr_handle *h, const double *joints_host, const int32_t *system_host, int64_t n, int32_t integrator,
+                int32_t precision, double *tip_host, double *R_host, int32_t *info_host);
+
+/* Obs.set_action x n_substeps (obs.py:166-183, ctr_reach_env.py:134-135) on caller arrays:
+ * joints f32 [6][n] in/out, action f32 [6][n], system i32 [n] or NULL. */
+int ctr_set_action(ctr_handle *h, float *joints_dev, const float *action_dev, const int32_t *system_dev, int64_t n,
+                   int32_t n_substeps, void *stream);
+
+/* Overwrite env state (testing / checkpoint restore): any pointer may be NULL (left unchanged).
+ * joints f32 [6][N], desired_goal f64 [3][N], system i32 [N], t i32 [N]; host pointers. */
+int ctr_set_state_host(ctr_handle *h, const float *joints, const double *desired_goal, const int32_t *system,
+                       const int32_t *t);
+
+/* CtrReachEnv.reset(goal, system) (ctr_reach_env.py:70-114).  mask u8 [N] or NULL (all envs); goal f64 [3][N]
+ * or NULL (sample, :98-101); system i32 [N] or NULL (sample uniformly, :95).  Writes joints, desired_*,
+ * starting_*, achieved, t = 0 and the observation buffers. */
+int ctr_reset(ctr_handle *h, const uint8_t *mask_dev, const double *goal_dev, const int32_t *system_dev, void *stream);
+
+/* CtrReachEnv.step (ctr_reach_env.py:124-158) for all N envs: action f32 [6][N] on the device.  Results land in
+ * the CTR_F_OBS / ACHIEVED_GOAL / DESIRED_GOAL / REWARD / DONE / SUCCESS / ERROR buffers. */
+int ctr_step(ctr_handle *h, const float *action_dev, void *stream);
+/* Same, with an arbitrary action layout: element (joint i, env e) is action_dev[i * stride_field + e * stride_env]
+ * (stride_field = N, stride_env = 1 is the SoA layout above; 1 and 6 is a row-major (N, 6) policy output). */
+int ctr_step_strided(ctr_handle *h, const float *action_dev, int64_t stride_field, int64_t stride_env, void *stream);
+
+/* The same call with HOST buffers (the end-to-end path): copies action [6][N] host->device, steps, and copies
+ * the results back.  Any output pointer may be NULL.  obs f64 [D][N], achieved/desired f64 [3][N],
+ * reward f64 [N], done/success u8 [N], error f64 [N]. */
+int ctr_step_host(ctr_handle *h, const float *action_host, double *obs_host, double *achieved_host, double *desired_host,
+                  double *reward_host, uint8_t *done_host, uint8_t *success_host, double *error_host);
+int ctr_reset_host(ctr_handle *h, double *obs_host, double *achieved_host, double *desired_host);
+
+/* CtrReachEnv.compute_reward (ctr_reach_env.py:160-170) on arbitrary batches (HER relabelling):
+ * achieved/desired f64 [3][m] -> reward f64 [m].  tol < 0 uses the handle's tolerance; mode < 0 the config's. */
+int ctr_compute_reward(ctr_handle *h, const double *achieved_dev, const double *desired_dev, int64_t m, double tol,
+                       int32_t mode, double *reward_dev, void *stream);
+/* HER relabel (extension): reward as above and obs[9:12] = new_desired - achieved, obs f64 [D][m]. */
+int ctr_relabel(ctr_handle *h, const double *achieved_dev, const double *new_desired_dev, int64_t m, double tol,
+                int32_t mode, double *reward_dev, double *obs_dev, void *stream);
+
+/* Episode statistics accumulated on the device since the last ctr_stats_reset: out8 (host) =
+ * [episodes, successes, sum final error, sum return, sum episode length, env steps, resets, goal-sampling draws].
+ * Multi-GPU callers all-reduce(SUM) these 8 doubles. */
+int ctr_stats(ctr_handle *h, double out8_host[8], void *stream);
+int ctr_stats_reset(ctr_handle *h, void *stream);
+
+/* FK work since the last ctr_stats_reset: [RHS evaluations, RK step attempts, sections, FK solves] (roofline
+ * accounting: algorithmic flops = nfev*120 + attempts*1290 + sections*200). */
+int ctr_work_counters(ctr_handle *h, double out4_host[4], void *stream);
+
+/* Measured FMA-pipe peak of `device` in TFLOP/s (register-resident FMA chains; precision = CTR_PRECISION_*):
+ * the roofline denominator of the FK kernels. */
+int ctr_measure_fma_peak(int32_t device, int32_t precision, double *tflops_out);
+
+/* Number of kernels launched by this handle so far (bench.py's gpu_launches claim). */
+int64_t ctr_launch_count(const ctr_handle *h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CTR_B200_H */

@@ -339,16 +339,20 @@ def sample_goal(rng, L):
 # observation / reward / flags / tolerance (envs/obs.py, obs_utils.py, ctr_reach_env.py, goal_tolerance.py)
 # ----------------------------------------------------------------------------------------------
 def joint_rep(joints, representation='egocentric'):
-    """[cos a, sin a, b] x 3 as float64 values of float32 arithmetic (obs_utils.py:41-53, 69-80)."""
+    """[cos a, sin a, b] x 3 (obs_utils.py:41-53, 69-80).
+
+    proprioceptive: float32 joints stay float32, so the trig is float32 arithmetic.
+    egocentric: prop2ego's np.diff(..., prepend=0) concatenates an int64 zero with the float32 joints, which promotes
+    to float64 -- the first differences and the trig are float64 arithmetic on float32-valued joints."""
     j = np.asarray(joints, dtype=np.float32)
     b, a = j[:3], j[3:]
     if representation == 'egocentric':
-        b = np.diff(b, prepend=np.float32(0))
-        a = np.diff(a, prepend=np.float32(0))
+        b = np.diff(b.astype(np.float64), prepend=0.0)
+        a = np.diff(a.astype(np.float64), prepend=0.0)
     rep = []
     for bi, ai in zip(b, a):
-        rep += [np.cos(np.float32(ai)), np.sin(np.float32(ai)), np.float32(bi)]
-    return np.array(rep, dtype=np.float32).astype(np.float64)
+        rep += [np.cos(ai), np.sin(ai), bi]
+    return np.array(rep).astype(np.float64)
 
 
 def get_obs(joints, desired, achieved, tol, system, num_systems=1, representation='egocentric'):
@@ -366,8 +370,16 @@ def compute_reward(achieved, desired, tol):
 
 
 def step_flags(achieved, desired, tol, t, max_steps):
-    """reward, done, is_success, error (ctr_reach_env.py:139-140, 155-156); t is the post-increment count."""
-    err = np.linalg.norm(np.asarray(desired) - np.asarray(achieved), axis=-1)
+    """reward, done, is_success, error (ctr_reach_env.py:139-140, 155-156); t is the post-increment count.
+
+    The reference takes the reward distance with norm(axis=-1) (unfused (x^2 + y^2) + z^2) but is_success / error with
+    the 1-D norm (a BLAS dot, whose fused/unfused summation is implementation defined): for 1-D inputs both calls are
+    repeated here verbatim; batches use the axis form throughout (the two can differ in the last ulp of `error`)."""
+    achieved, desired = np.asarray(achieved), np.asarray(desired)
+    if achieved.ndim == 1:
+        err = np.linalg.norm(desired - achieved)
+    else:
+        err = np.linalg.norm(desired - achieved, axis=-1)
     reward = compute_reward(achieved, desired, tol)
     done = (reward == 0) | (np.asarray(t) >= max_steps)
     return reward, done, err < tol, err
