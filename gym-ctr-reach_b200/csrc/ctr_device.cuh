@@ -358,6 +358,7 @@ __device__ __forceinline__ void fk_group(const LaneId& id, bool valid, const dou
         if (INTEG == 1 && steps_left == 1) t_new = tf;
         const double h_d = t_new - t;
         const T h = (T)h_d;
+        if (INTEG == 0) h_abs = fabs(h_d);   // rk.py:136-137: the factor below scales the step actually taken
 
         T ynew[6];
         bool accept = true;
