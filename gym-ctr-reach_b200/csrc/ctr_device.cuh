@@ -26,6 +26,7 @@ constexpr int MAX_ATTEMPTS = 4000;  // hard cap on RK step attempts per FK (term
 // ---- per-system constants staged once per block in shared memory --------------------------------------------
 struct SysConst {
     double L[3], Lc[3], EI[3], GJ[3], Ux[3], Uy[3];  // derived tube constants (Tube.py:14-15, Segment.py:57-59)
+    double der[15];                                  // EI, EI Ux, EI Uy, (EI/GJ) Ux, (EI/GJ) Uy per tube (see DER_*)
     float low[6], high[6];                           // joint Box bounds, float32 (obs.py:59-75)
     float d10, d21;                                  // f32(L1 - L0), f32(L2 - L1) (obs.py:181, NEP-50 weak python float)
     float Lf[3];                                     // f32(L_i) for the goal-sampling predicate (obs.py:198-200)
@@ -63,22 +64,129 @@ __device__ __forceinline__ T group_sum(const LaneId& id, T p) {
 }
 
 // ---- math helpers, overloaded on the state type --------------------------------------------------------------
-__device__ __forceinline__ void sincos_t(double x, double* s, double* c) { sincos(x, s, c); }
-__device__ __forceinline__ void sincos_t(float x, float* s, float* c) { sincosf(x, s, c); }
 __device__ __forceinline__ double fma_t(double a, double b, double c) { return fma(a, b, c); }
 __device__ __forceinline__ float fma_t(float a, float b, float c) { return fmaf(a, b, c); }
 __device__ __forceinline__ double abs_t(double a) { return fabs(a); }
 __device__ __forceinline__ float abs_t(float a) { return fabsf(a); }
 __device__ __forceinline__ double max_t(double a, double b) { return fmax(a, b); }
 __device__ __forceinline__ float max_t(float a, float b) { return fmaxf(a, b); }
-__device__ __forceinline__ double rcp_t(double a) { return 1.0 / a; }
+
+// 1/x for normal positive x: MUFU.RCP64H seed + two Newton steps (relative error < 2^-52; no special cases, no
+// slow-path call -- the compiler's '/' costs ~3x as much and a branch).
+__device__ __forceinline__ double rcp_fast(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    return r;
+}
+__device__ __forceinline__ double rcp_t(double a) { return rcp_fast(a); }
 __device__ __forceinline__ float rcp_t(float a) { return 1.0f / a; }
 
-// ---- section geometry (Segment.py:6-61) -- IEEE float64, explicit _rn intrinsics so nothing is contracted ----
-struct Geometry {
-    double pts[10];      // sorted transition points (dynamic index -> local memory; touched once per section)
-    double beta[3], dtip[3], dc[3];
-    double bmin;
+// sqrt(x) for normal positive x (MUFU.RSQ64H seed + Goldschmidt, final residual correction)
+__device__ __forceinline__ double sqrt_fast(double x) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    double g = x * y, h = 0.5 * y;
+    double r = fma(-h, g, 0.5);
+    g = fma(g, r, g);
+    h = fma(h, r, h);
+    r = fma(-h, g, 0.5);
+    g = fma(g, r, g);
+    h = fma(h, r, h);
+    r = fma(-g, g, x);
+    return fma(r, h, g);
+}
+
+// x^(-1/10) for x in [1e-30, 1e30]: float MUFU seed (lg2/ex2, ~1e-6) + two Newton steps on y^-10 = x
+// (y <- y (1 + (1 - x y^10) / 10), error -> 5.5 e^2), i.e. full double precision in 14 FP64 ops.  Replaces the
+// pow(err, -0.2) / pow(., 0.2) of the step-size controller (rk.py:147, common.py:127), whose argument is err^2 here.
+__device__ __forceinline__ double pow_m01(double x) {
+    double y = (double)exp2f(-0.1f * __log2f((float)x));
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        double y2 = y * y, y4 = y2 * y2, y8 = y4 * y4, y10 = y8 * y2;
+        double e = fma(-x, y10, 1.0);
+        y = fma(y * 0.1, e, y);
+    }
+    return y;
+}
+
+// sin / cos of a double with a 3-term Cody-Waite reduction (exact first product for |n| < 2^20) and the fdlibm
+// kernel polynomials on [-pi/4, pi/4]; <= 1 ulp for |x| < 1e3, <= 2 ulp up to 1e5; larger arguments take the
+// library path.  21 FP64 ops, no local memory, no call.
+__device__ __forceinline__ void sincos_t(double x, double* s, double* c) {
+    if (__builtin_expect(!(fabs(x) < 1.0e5), 0)) {
+        sincos(x, s, c);
+        return;
+    }
+    const double t = fma(x, 0.63661977236758138243, 6755399441055744.0);
+    const int q = __double2loint(t);
+    const double n = t - 6755399441055744.0;
+    double r = fma(-n, 1.57079632673412561417e+00, x);
+    r = fma(-n, 6.07710050630396597660e-11, r);
+    r = fma(-n, 2.02226624871116645580e-21, r);
+    const double z = r * r;
+    double ps = fma(z, 1.58969099521155010221e-10, -2.50507602534068634195e-08);
+    double pc = fma(z, -1.13596475577881948265e-11, 2.08757232129817482790e-09);
+    ps = fma(z, ps, 2.75573137070700676789e-06);
+    pc = fma(z, pc, -2.75573143513906633035e-07);
+    ps = fma(z, ps, -1.98412698298579493134e-04);
+    pc = fma(z, pc, 2.48015872894767294178e-05);
+    ps = fma(z, ps, 8.33333333332248946124e-03);
+    pc = fma(z, pc, -1.38888888888741095749e-03);
+    ps = fma(z, ps, -1.66666666666666324348e-01);
+    pc = fma(z, pc, 4.16666666666666019037e-02);
+    double sn = fma(r * z, ps, r);
+    double cs = fma(z * z, pc, fma(z, -0.5, 1.0));
+    if (q & 1) {
+        const double tmp = sn;
+        sn = cs;
+        cs = -tmp;
+    }
+    if (q & 2) {
+        sn = -sn;
+        cs = -cs;
+    }
+    *s = sn;
+    *c = cs;
+}
+__device__ __forceinline__ void sincos_t(float x, float* s, float* c) { sincosf(x, s, c); }
+
+// Dormand-Prince 5(4) tableau (rk.py: class RK45) in constant memory: used as c[bank][offset] operands, so the
+// hot loop materialises no immediates (the previous build spent 18 % of its issue slots on UMOV for these).
+enum { A21 = 0, A31, A32, A41, A42, A43, A51, A52, A53, A54, A61, A62, A63, A64, A65, B1, B3, B4, B5, B6, E1, E3, E4, E5,
+       E6, E7, DP_NCOEF };
+__constant__ double c_dp64[DP_NCOEF] = {
+    1.0 / 5, 3.0 / 40, 9.0 / 40, 44.0 / 45, -56.0 / 15, 32.0 / 9, 19372.0 / 6561, -25360.0 / 2187, 64448.0 / 6561,
+    -212.0 / 729, 9017.0 / 3168, -355.0 / 33, 46732.0 / 5247, 49.0 / 176, -5103.0 / 18656, 35.0 / 384, 500.0 / 1113,
+    125.0 / 192, -2187.0 / 6784, 11.0 / 84, -71.0 / 57600, 71.0 / 16695, -71.0 / 1920, 17253.0 / 339200, -22.0 / 525,
+    1.0 / 40};
+__constant__ float c_dp32[DP_NCOEF] = {
+    (float)(1.0 / 5), (float)(3.0 / 40), (float)(9.0 / 40), (float)(44.0 / 45), (float)(-56.0 / 15), (float)(32.0 / 9),
+    (float)(19372.0 / 6561), (float)(-25360.0 / 2187), (float)(64448.0 / 6561), (float)(-212.0 / 729),
+    (float)(9017.0 / 3168), (float)(-355.0 / 33), (float)(46732.0 / 5247), (float)(49.0 / 176), (float)(-5103.0 / 18656),
+    (float)(35.0 / 384), (float)(500.0 / 1113), (float)(125.0 / 192), (float)(-2187.0 / 6784), (float)(11.0 / 84),
+    (float)(-71.0 / 57600), (float)(71.0 / 16695), (float)(-71.0 / 1920), (float)(17253.0 / 339200), (float)(-22.0 / 525),
+    (float)(1.0 / 40)};
+template <typename T> __device__ __forceinline__ T dpc(int i);
+template <> __device__ __forceinline__ double dpc<double>(int i) { return c_dp64[i]; }
+template <> __device__ __forceinline__ float dpc<float>(int i) { return c_dp32[i]; }
+
+// ---- section table (Segment.py:6-61) -- IEEE float64, explicit _rn intrinsics so nothing is contracted -------
+// Built once per FK by the lane group into its shared-memory slot: the integration spans [t0, tf] of the kept
+// sections (model.py:137-151) and, per section, which tubes are present / curved.  The main loop then only indexes it.
+constexpr int MAXSEC = 9;
+enum { DER_EI = 0, DER_EIUX = 3, DER_EIUY = 6, DER_KX = 9, DER_KY = 12, DER_COUNT = 15 };
+
+struct GroupScratch {            // 312 B: 78 words, so the 10 groups of a warp hit distinct bank pairs
+    double t0[MAXSEC], tf[MAXSEC];
+    int pat[MAXSEC];             // bits 0-2: tube present, bits 3-5: tube curved
+    int nsec;                    // kept sections | (zero-length spans << 8)
+    double der[DER_COUNT];       // EI_m, EI_m Ux_m, EI_m Uy_m, (EI_m / GJ_m) Ux_m, (EI_m / GJ_m) Uy_m
+    double pad;
 };
 
 __device__ __forceinline__ void cswap(double& a, double& b) {
@@ -87,19 +195,21 @@ __device__ __forceinline__ void cswap(double& a, double& b) {
     b = hi;
 }
 
-__device__ __forceinline__ void build_geometry(const double* L, const double* Lc, const double* beta, Geometry& G) {
-    double p[10];
+// L, Lc: tube lengths / curved lengths; beta: float64 joint extensions.  All lanes of the group compute the same
+// values; `writer` (one lane) stores them.  Ends with __syncwarp() so the group can read the table.
+__device__ __forceinline__ void build_sections(const double* L, const double* Lc, const double* beta, GroupScratch& gs,
+                                               bool writer) {
+    double p[10], dtip[3], dc[3];
     p[0] = 0.0;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-        G.beta[i] = beta[i];
-        G.dtip[i] = __dadd_rn(L[i], beta[i]);          // Segment.py:12
-        G.dc[i] = __dsub_rn(G.dtip[i], Lc[i]);         // Segment.py:13
+        dtip[i] = __dadd_rn(L[i], beta[i]);        // Segment.py:12
+        dc[i] = __dsub_rn(dtip[i], Lc[i]);         // Segment.py:13
         p[1 + i] = beta[i];
-        p[4 + i] = G.dc[i];
-        p[7 + i] = G.dtip[i];
+        p[4 + i] = dc[i];
+        p[7 + i] = dtip[i];
     }
-    G.bmin = fmin(fmin(beta[0], beta[1]), beta[2]);    // Segment.py:53 min(base)
+    const double bmin = fmin(fmin(beta[0], beta[1]), beta[2]);   // Segment.py:53 min(base)
     // 29-comparator sorting network for 10 keys (Segment.py:15-16 np.sort; tie order is irrelevant)
 #define CS(a, b) cswap(p[a], p[b])
     CS(0, 8); CS(1, 9); CS(2, 7); CS(3, 5); CS(4, 6);
@@ -111,8 +221,45 @@ __device__ __forceinline__ void build_geometry(const double* L, const double* Lc
     CS(2, 3); CS(4, 5); CS(6, 7);
     CS(3, 4); CS(5, 6);
 #undef CS
+    double cum = 0.0, prevS = 0.0;
+    int m = 0, skipped = 0;
 #pragma unroll
-    for (int i = 0; i < 10; ++i) G.pts[i] = p[i];
+    for (int k = 0; k < 9; ++k) {
+        const double lo = p[k], hi = p[k + 1];
+        const double len = __dmul_rn(1e-5, floor(__dmul_rn(1e5, __dsub_rn(hi, lo))));   // Segment.py:16
+        cum = __dadd_rn(cum, len);                                                       // Segment.py:52 (len == 0 adds 0)
+        const double S = __dadd_rn(cum, bmin);                                           // Segment.py:53
+        if (len != 0.0 && S > 0.0) {                                                     // Segment.py:46,53
+            int pat = 0;
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                const bool present = (beta[i] <= lo) && (hi <= dtip[i]);                 // Segment.py:23-41 (value form)
+                const bool curved = present && (dc[i] <= lo);                            // Segment.py:42-43
+                pat |= (present ? 1 : 0) << i;
+                pat |= (curved ? 8 : 0) << i;
+            }
+            double t0 = prevS;
+            double tf = __dsub_rn(S, 1e-6);                                              // model.py:141
+            if (tf < t0) {                                                               // model.py:145-151: sorted span
+                const double z = t0;
+                t0 = tf;
+                tf = z;
+            }
+            prevS = S;
+            if (tf == t0) {
+                skipped += 1;                  // zero-length span: the solver returns y0 after one RHS call (base.py)
+            } else {
+                if (writer) {
+                    gs.t0[m] = t0;
+                    gs.tf[m] = tf;
+                    gs.pat[m] = pat;
+                }
+                m += 1;
+            }
+        }
+    }
+    if (writer) gs.nsec = m | (skipped << 8);
+    __syncwarp();
 }
 
 // ---- per-section constants in the lane-rotated form -----------------------------------------------------------
@@ -121,104 +268,54 @@ struct Section {
     T Ao, Bo;   // A_j, B_j of the lane's own tube:   A_m = EI_m Ux_m / sum(EI),  B_m = EI_m Uy_m / sum(EI)
     T An, Bn;   // tube (j+1)%3
     T Ap, Bp;   // tube (j+2)%3
-    T kx, ky;   // (EI_j / GJ_j) * Ux_j , (EI_j / GJ_j) * Uy_j   (0 when tube j is absent: model.py:97-99)
+    T kx, ky;   // (EI_j / GJ_j) * Ux_j , (EI_j / GJ_j) * Uy_j   (0 when tube j is absent or straight: model.py:97-101)
     T present;  // 1 when tube j exists on this section (alpha_j' = uz_j), else 0
 };
 
-template <typename T>
-__device__ __forceinline__ void make_section(const Geometry& G, const double* EI, const double* GJ, const double* Ux,
-                                             const double* Uy, double lo, double hi, int j, Section<T>& sc) {
-    double ei[3], a[3], b[3];
-    bool curved[3];
-#pragma unroll
-    for (int m = 0; m < 3; ++m) {
-        bool present = (G.beta[m] <= lo) && (hi <= G.dtip[m]);   // Segment.py:23-41 (value form)
-        curved[m] = present && (G.dc[m] <= lo);                  // Segment.py:42-43
-        ei[m] = present ? EI[m] : 0.0;
-    }
-    double inv = 1.0 / (ei[0] + ei[1] + ei[2]);                  // model.py:87
-#pragma unroll
-    for (int m = 0; m < 3; ++m) {
-        a[m] = curved[m] ? ei[m] * Ux[m] * inv : 0.0;
-        b[m] = curved[m] ? ei[m] * Uy[m] * inv : 0.0;
-    }
-    sc.Ao = (T)pick3(j, a[0], a[1], a[2]);
-    sc.Bo = (T)pick3(j, b[0], b[1], b[2]);
-    sc.An = (T)pick3(j, a[1], a[2], a[0]);
-    sc.Bn = (T)pick3(j, b[1], b[2], b[0]);
-    sc.Ap = (T)pick3(j, a[2], a[0], a[1]);
-    sc.Bp = (T)pick3(j, b[2], b[0], b[1]);
-    double eij = pick3(j, ei[0], ei[1], ei[2]);
-    double gjj = pick3(j, GJ[0], GJ[1], GJ[2]);
-    bool cj = pick3(j, curved[0], curved[1], curved[2]);
-    double k = (eij != 0.0) ? eij / gjj : 0.0;                   // model.py:101
-    sc.kx = (T)(cj ? k * pick3(j, Ux[0], Ux[1], Ux[2]) : 0.0);
-    sc.ky = (T)(cj ? k * pick3(j, Uy[0], Uy[1], Uy[2]) : 0.0);
-    sc.present = (eij != 0.0) ? (T)1 : (T)0;
-}
-
 // ---- ODE right-hand side (model.py:72-117), one lane's slice ------------------------------------------------
 // Y = {uz_j, alpha_j, r_j, R_j0, R_j1, R_j2} -> D = d/ds of the same.  Executed by the full warp.
+// tg keeps the sin / cos of the two angle differences this lane uses: when a new section starts at the state the
+// last evaluation was made at (FSAL), only the algebra is redone with the new constants (do_trig = false).
 template <typename T>
-__device__ __forceinline__ void rhs(const LaneId& id, const Section<T>& sc, const T (&Y)[6], T (&D)[6]) {
-    T a_next = __shfl_sync(FULL, Y[1], id.lnext);
-    T s_o, c_o;
-    sincos_t(Y[1] - a_next, &s_o, &c_o);                 // angle alpha_j - alpha_{j+1}
-    T c_p = __shfl_sync(FULL, c_o, id.lprev);            // cos(alpha_{j-1} - alpha_j)
-    T s_p = __shfl_sync(FULL, s_o, id.lprev);            // sin(alpha_{j-1} - alpha_j) = -sin(alpha_j - alpha_{j-1})
-    // model.py:87-94 with cos(0) = 1, sin(0) = 0 folded
-    T ux = fma_t(sc.An, c_o, sc.Ao);
-    ux = fma_t(sc.Bn, s_o, ux);
-    ux = fma_t(sc.Ap, c_p, ux);
-    ux = fma_t(-sc.Bp, s_p, ux);
-    T uy = fma_t(-sc.An, s_o, sc.Bo);
-    uy = fma_t(sc.Bn, c_o, uy);
-    uy = fma_t(sc.Ap, s_p, uy);
-    uy = fma_t(sc.Bp, c_p, uy);
+struct Trig {
+    T co, so;   // cos / sin(alpha_j - alpha_{j+1})
+    T cp, sp;   // cos / sin(alpha_{j-1} - alpha_j)
+};
+
+template <typename T>
+__device__ __forceinline__ void rhs(const LaneId& id, const Section<T>& sc, bool do_trig, Trig<T>& tg, const T (&Y)[6],
+                                    T (&D)[6]) {
+    if (do_trig) {   // warp-uniform
+        const T a_next = __shfl_sync(FULL, Y[1], id.lnext);
+        sincos_t(Y[1] - a_next, &tg.so, &tg.co);
+        tg.cp = __shfl_sync(FULL, tg.co, id.lprev);
+        tg.sp = __shfl_sync(FULL, tg.so, id.lprev);
+    }
+    // model.py:87-94 with cos(0) = 1, sin(0) = 0 folded; sin(alpha_j - alpha_{j-1}) = -sp
+    T ux = fma_t(sc.An, tg.co, sc.Ao);
+    T uy = fma_t(-sc.An, tg.so, sc.Bo);
+    ux = fma_t(sc.Bn, tg.so, ux);
+    uy = fma_t(sc.Bn, tg.co, uy);
+    ux = fma_t(sc.Ap, tg.cp, ux);
+    uy = fma_t(sc.Ap, tg.sp, uy);
+    ux = fma_t(-sc.Bp, tg.sp, ux);
+    uy = fma_t(sc.Bp, tg.cp, uy);
     D[0] = fma_t(ux, sc.ky, -(uy * sc.kx));              // model.py:101  (0 when absent: kx = ky = 0)
     D[1] = sc.present * Y[0];                            // model.py:99,102
-    T ux0 = __shfl_sync(FULL, ux, id.l0);
-    T uy0 = __shfl_sync(FULL, uy, id.l0);
-    T uz0 = __shfl_sync(FULL, Y[0], id.l0);
+    const T ux0 = __shfl_sync(FULL, ux, id.l0);
+    const T uy0 = __shfl_sync(FULL, uy, id.l0);
+    const T uz0 = __shfl_sync(FULL, Y[0], id.l0);
     D[2] = Y[5];                                         // r' = R e3          (model.py:108)
     D[3] = fma_t(Y[4], uz0, -(Y[5] * uy0));              // R' = R u_hat, row j (model.py:107,109)
     D[4] = fma_t(Y[5], ux0, -(Y[3] * uz0));
     D[5] = fma_t(Y[3], uy0, -(Y[4] * ux0));
 }
 
-// Dormand-Prince 5(4) tableau (rk.py: class RK45)
-#define DP_A21 (1.0 / 5)
-#define DP_A31 (3.0 / 40)
-#define DP_A32 (9.0 / 40)
-#define DP_A41 (44.0 / 45)
-#define DP_A42 (-56.0 / 15)
-#define DP_A43 (32.0 / 9)
-#define DP_A51 (19372.0 / 6561)
-#define DP_A52 (-25360.0 / 2187)
-#define DP_A53 (64448.0 / 6561)
-#define DP_A54 (-212.0 / 729)
-#define DP_A61 (9017.0 / 3168)
-#define DP_A62 (-355.0 / 33)
-#define DP_A63 (46732.0 / 5247)
-#define DP_A64 (49.0 / 176)
-#define DP_A65 (-5103.0 / 18656)
-#define DP_B1 (35.0 / 384)
-#define DP_B3 (500.0 / 1113)
-#define DP_B4 (125.0 / 192)
-#define DP_B5 (-2187.0 / 6784)
-#define DP_B6 (11.0 / 84)
-#define DP_E1 (-71.0 / 57600)
-#define DP_E3 (71.0 / 16695)
-#define DP_E4 (-71.0 / 1920)
-#define DP_E5 (17253.0 / 339200)
-#define DP_E6 (-22.0 / 525)
-#define DP_E7 (1.0 / 40)
-
-__device__ __forceinline__ double ulp_up(double t) {  // |nextafter(t, +inf) - t|   (rk.py:116)
-    long long b = __double_as_longlong(t);
-    double n = (t >= 0.0) ? __longlong_as_double(b + 1) : __longlong_as_double(b - 1);
-    if (t == 0.0) n = __longlong_as_double(1);
-    return fabs(n - t);
+// 10 * |nextafter(t, +inf) - t| (rk.py:116) for the t of this path (non-negative except the rare reversed first span)
+__device__ __forceinline__ double min_step_of(double t) {
+    const int e = __double2hiint(t) & 0x7ff00000;
+    const int u = e > 0x03400000 ? e - 0x03400000 : 0;
+    return 10.0 * __hiloint2double(u, 0);
 }
 
 struct FkInfo {
@@ -226,228 +323,224 @@ struct FkInfo {
 };
 
 // ---- forward kinematics (model.py:30-70, 119-174) for the lane group ----------------------------------------
-// INTEG 0: scipy RK45 restated (rk.py rk_step/_step_impl, common.py select_initial_step), per-env adaptive.
-// INTEG 1: classical RK4, rk4_steps per section.
-// beta/alpha: float64 joint values (float32 joints promoted exactly, model.py:50-61).
-// On return lane j holds y = {uz_j, alpha_j, r_j, R_j0..2} at the tip.
-template <typename T, int INTEG>
-__device__ __forceinline__ void fk_group(const LaneId& id, bool valid, const double* L, const double* Lc,
-                                         const double* EI, const double* GJ, const double* Ux, const double* Uy,
-                                         const double* beta, const double* alpha, double rtol_d, double atol_d,
-                                         int rk4_steps, T (&y)[6], FkInfo& info) {
-    Geometry G;
-    build_geometry(L, Lc, beta, G);
-    const int j = id.j;
-    {   // initial state (model.py:56-64): uz = 0, alpha = joint[3:], r = 0, R = Rz(alpha_0)
-        double s0, c0;
-        sincos(alpha[0], &s0, &c0);
-        y[0] = (T)0;
-        y[1] = (T)pick3(j, alpha[0], alpha[1], alpha[2]);
-        y[2] = (T)0;
-        y[3] = (T)pick3(j, c0, s0, 0.0);
-        y[4] = (T)pick3(j, -s0, c0, 0.0);
-        y[5] = (T)pick3(j, 0.0, 0.0, 1.0);
+// Control flow is warp-synchronous: every shuffle sits at a warp-uniform program point; per-environment decisions
+// (new section, accept / reject, finished) are predicated.  The stages are unrolled (a rolled stage loop makes ptxas
+// copy the whole k-array set at every stage), so rhs() is kept small: no library calls, no slow paths inlined.
+
+template <typename T>
+__device__ __forceinline__ void initial_state(int j, const double* alpha, T (&y)[6]) {
+    // model.py:56-64: uz = 0, alpha = joint[3:], r = 0, R = Rz(alpha_0)
+    double s0, c0;
+    sincos(alpha[0], &s0, &c0);
+    y[0] = (T)0;
+    y[1] = (T)pick3(j, alpha[0], alpha[1], alpha[2]);
+    y[2] = (T)0;
+    y[3] = (T)pick3(j, c0, s0, 0.0);
+    y[4] = (T)pick3(j, -s0, c0, 0.0);
+    y[5] = (T)pick3(j, 0.0, 0.0, 1.0);
+}
+
+// Next kept section of this lane's environment (model.py:137-151).  Returns true when a section was started.
+template <typename T>
+__device__ __forceinline__ bool advance_section(const GroupScratch& gs, const double* der, int nsec, int mo, int mn,
+                                                int mp, int& ksec, bool& done, double& t, double& tf, Section<T>& sc) {
+    if (ksec >= nsec) {
+        done = true;
+        return false;
     }
-    info.nfev = info.nacc = info.nrej = info.nsec = info.failed = 0;
+    t = gs.t0[ksec];
+    tf = gs.tf[ksec];
+    const int pat = gs.pat[ksec];
+    ksec += 1;
+    const double e0 = (pat & 1) ? der[DER_EI + 0] : 0.0;
+    const double e1 = (pat & 2) ? der[DER_EI + 1] : 0.0;
+    const double e2 = (pat & 4) ? der[DER_EI + 2] : 0.0;
+    const double inv = rcp_fast((e0 + e1) + e2);                     // model.py:87 (a kept section has >= 1 tube)
+    const bool co = (pat >> (3 + mo)) & 1, cn = (pat >> (3 + mn)) & 1, cp = (pat >> (3 + mp)) & 1;
+    sc.Ao = (T)(co ? der[DER_EIUX + mo] * inv : 0.0);
+    sc.Bo = (T)(co ? der[DER_EIUY + mo] * inv : 0.0);
+    sc.An = (T)(cn ? der[DER_EIUX + mn] * inv : 0.0);
+    sc.Bn = (T)(cn ? der[DER_EIUY + mn] * inv : 0.0);
+    sc.Ap = (T)(cp ? der[DER_EIUX + mp] * inv : 0.0);
+    sc.Bp = (T)(cp ? der[DER_EIUY + mp] * inv : 0.0);
+    sc.kx = (T)(co ? der[DER_KX + mo] : 0.0);
+    sc.ky = (T)(co ? der[DER_KY + mo] : 0.0);
+    sc.present = ((pat >> mo) & 1) ? (T)1 : (T)0;
+    return true;
+}
+
+// INTEG 0: scipy RK45 restated (rk.py rk_step/_step_impl, common.py select_initial_step), per-env adaptive.
+// On return lane j holds y = {uz_j, alpha_j, r_j, R_j0..2} at the tip.
+template <typename T>
+__device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const GroupScratch& gs, const double* der,
+                                        const double* alpha, double rtol_d, double atol_d, T (&y)[6], FkInfo& info) {
+    const int j = id.j;
+    const int mn = (j == 2) ? 0 : j + 1, mp = (j == 0) ? 2 : j - 1;
+    initial_state<T>(j, alpha, y);
+    const int packed = valid ? gs.nsec : 0;
+    const int nsec = packed & 0xff;
+    info.nfev = info.nsec = packed >> 8;          // zero-length spans: one RHS call each, no step
+    info.nacc = info.nrej = info.failed = 0;
     const T rtol = (T)rtol_d, atol = (T)atol_d;
     Section<T> sc;
     sc.Ao = sc.Bo = sc.An = sc.Bn = sc.Ap = sc.Bp = sc.kx = sc.ky = sc.present = (T)0;
-    T f[6] = {0, 0, 0, 0, 0, 0};   // derivative at (t, y)  (FSAL: rk.py:170)
-    int k = -1;
-    double cum = 0.0, prevS = 0.0;
+    Trig<T> tg;
+    tg.co = tg.cp = (T)1;
+    tg.so = tg.sp = (T)0;
+    T f[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) f[i] = (T)0;
+    int ksec = 0, attempts = 0;
     double t = 0.0, tf = 0.0, h_abs = 0.0;
     bool done = !valid, need_sec = true, rejected = false;
-    int steps_left = 0;
-    int attempts = 0;
+    bool first = true;   // warp-uniform: no RHS has been evaluated yet, so slot 0 needs the trigonometry
 
-    while (true) {
-        // ---- advance to the next kept section (Segment.py:46-53, model.py:137-151); scalar, no shuffles
+    for (;;) {
         bool init = false;
-        while (!done && need_sec) {
-            bool found = false;
-            double lo = 0.0, hi = 0.0, S = 0.0;
-            while (++k < 9) {
-                lo = G.pts[k];
-                hi = G.pts[k + 1];
-                double len = __dmul_rn(1e-5, floor(__dmul_rn(1e5, __dsub_rn(hi, lo))));   // Segment.py:16
-                if (len == 0.0) continue;                                                  // Segment.py:46
-                cum = __dadd_rn(cum, len);                                                 // Segment.py:52
-                S = __dadd_rn(cum, G.bmin);                                                // Segment.py:53
-                if (!(S > 0.0)) continue;
-                found = true;
-                break;
-            }
-            if (!found) {
-                done = true;
-                break;
-            }
-            make_section<T>(G, EI, GJ, Ux, Uy, lo, hi, j, sc);
-            double t0 = prevS;
-            tf = __dsub_rn(S, 1e-6);                      // model.py:141
-            if (tf < t0) {                                // model.py:145-151: sorted span, integrate (min, max)
-                double z = t0;
-                t0 = tf;
-                tf = z;
-            }
-            prevS = S;
-            info.nsec += 1;
-            t = t0;
-            if (tf == t0) {                               // zero-length span: solver returns y0 (base.py step())
-                info.nfev += 1;
-                continue;
-            }
-            need_sec = false;
-            init = true;
-            rejected = false;
-            if (INTEG == 1) {
-                h_abs = (tf - t0) / (double)rk4_steps;
-                steps_left = rk4_steps;
+        if (__any_sync(FULL, need_sec && !done)) {
+            if (need_sec && !done) {
+                init = advance_section<T>(gs, der, nsec, j, mn, mp, ksec, done, t, tf, sc);
+                if (init) {
+                    need_sec = false;
+                    rejected = false;
+                    info.nsec += 1;
+                }
             }
         }
         if (!__any_sync(FULL, !done)) break;
+        const bool any_init = __any_sync(FULL, init);
+        const bool active = !done;
 
-        if (INTEG == 0) {
-            // ---- RungeKutta.__init__: f0 and select_initial_step (rk.py:93-101, common.py:68-134)
-            if (__any_sync(FULL, init)) {
-                T f0[6], f1[6], y1[6], rs[6];
-                rhs<T>(id, sc, y, f0);
-                T p0 = 0, p1 = 0;
-#pragma unroll
-                for (int i = 0; i < 6; ++i) {
-                    rs[i] = rcp_t(fma_t(abs_t(y[i]), rtol, atol));     // 1 / scale
-                    T a = y[i] * rs[i], b = f0[i] * rs[i];
-                    p0 = fma_t(a, a, p0);
-                    p1 = fma_t(b, b, p1);
-                }
-                double d0 = sqrt((double)group_sum(id, p0) * (1.0 / 18.0));   // common.py:63-65 RMS norm
-                double d1 = sqrt((double)group_sum(id, p1) * (1.0 / 18.0));
-                double interval = fabs(tf - t);
-                double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
-                h0 = fmin(h0, interval);
-                T h0t = (T)h0;
-#pragma unroll
-                for (int i = 0; i < 6; ++i) y1[i] = fma_t(h0t, f0[i], y[i]);
-                rhs<T>(id, sc, y1, f1);
-                T p2 = 0;
-#pragma unroll
-                for (int i = 0; i < 6; ++i) {
-                    T c = (f1[i] - f0[i]) * rs[i];
-                    p2 = fma_t(c, c, p2);
-                }
-                double d2 = sqrt((double)group_sum(id, p2) * (1.0 / 18.0)) / h0;
-                double h1;
-                if (d1 <= 1e-15 && d2 <= 1e-15) h1 = fmax(1e-6, h0 * 1e-3);
-                else h1 = pow(0.01 / fmax(d1, d2), 0.2);
-                if (init) {
-                    h_abs = fmin(fmin(100.0 * h0, h1), interval);
-                    info.nfev += 2;
-#pragma unroll
-                    for (int i = 0; i < 6; ++i) f[i] = f0[i];
-                }
-            }
-        }
-
-        const bool active = !done;   // every lane that is not done has a live section here
-        // ---- one step attempt (rk.py:108-178)
-        double min_step = 10.0 * ulp_up(t);
-        if (INTEG == 0) {
-            if (!rejected && h_abs < min_step) h_abs = min_step;
-        }
-        double t_new = t + h_abs;
-        if (t_new - tf > 0.0) t_new = tf;
-        if (INTEG == 1 && steps_left == 1) t_new = tf;
-        const double h_d = t_new - t;
-        const T h = (T)h_d;
-        if (INTEG == 0) h_abs = fabs(h_d);   // rk.py:136-137: the factor below scales the step actually taken
-
-        T ynew[6];
-        bool accept = true;
-        double factor = 1.0;
-        if (INTEG == 0) {
-            T k2[6], k3[6], k4[6], k5[6], k6[6], k7[6], Y[6];
-#pragma unroll
-            for (int i = 0; i < 6; ++i) Y[i] = fma_t(h * (T)DP_A21, f[i], y[i]);
-            rhs<T>(id, sc, Y, k2);
-#pragma unroll
-            for (int i = 0; i < 6; ++i) Y[i] = fma_t(h, fma_t((T)DP_A32, k2[i], (T)DP_A31 * f[i]), y[i]);
-            rhs<T>(id, sc, Y, k3);
-#pragma unroll
-            for (int i = 0; i < 6; ++i)
-                Y[i] = fma_t(h, fma_t((T)DP_A43, k3[i], fma_t((T)DP_A42, k2[i], (T)DP_A41 * f[i])), y[i]);
-            rhs<T>(id, sc, Y, k4);
-#pragma unroll
-            for (int i = 0; i < 6; ++i)
-                Y[i] = fma_t(h, fma_t((T)DP_A54, k4[i], fma_t((T)DP_A53, k3[i], fma_t((T)DP_A52, k2[i], (T)DP_A51 * f[i]))), y[i]);
-            rhs<T>(id, sc, Y, k5);
-#pragma unroll
-            for (int i = 0; i < 6; ++i)
-                Y[i] = fma_t(h, fma_t((T)DP_A65, k5[i], fma_t((T)DP_A64, k4[i], fma_t((T)DP_A63, k3[i],
-                             fma_t((T)DP_A62, k2[i], (T)DP_A61 * f[i])))), y[i]);
-            rhs<T>(id, sc, Y, k6);
-#pragma unroll
-            for (int i = 0; i < 6; ++i)
-                ynew[i] = fma_t(h, fma_t((T)DP_B6, k6[i], fma_t((T)DP_B5, k5[i], fma_t((T)DP_B4, k4[i],
-                                fma_t((T)DP_B3, k3[i], (T)DP_B1 * f[i])))), y[i]);
-            rhs<T>(id, sc, ynew, k7);
-            T pe = 0;
+        // ---- RungeKutta.__init__: f0 and select_initial_step (rk.py:93-101, common.py:68-134); run by the whole warp
+        //      whenever at least one environment starts a section (its FSAL derivative belongs to the old constants)
+        if (any_init) {
+            T D[6], rs[6], Y[6];
+            rhs<T>(id, sc, first, tg, y, D);                // f0 = f(t0, y0); trigonometry reused unless first
+            T p0 = 0, p1 = 0;
 #pragma unroll
             for (int i = 0; i < 6; ++i) {
-                T e = fma_t((T)DP_E7, k7[i], fma_t((T)DP_E6, k6[i], fma_t((T)DP_E5, k5[i], fma_t((T)DP_E4, k4[i],
-                            fma_t((T)DP_E3, k3[i], (T)DP_E1 * f[i])))));
-                T sc_i = fma_t(max_t(abs_t(y[i]), abs_t(ynew[i])), rtol, atol);     // rk.py:141
-                T q = (e * h) * rcp_t(sc_i);
-                pe = fma_t(q, q, pe);
+                if (init) f[i] = D[i];
+                rs[i] = rcp_t(fma_t(abs_t(y[i]), rtol, atol));     // 1 / scale
+                const T a = y[i] * rs[i], b = D[i] * rs[i];
+                p0 = fma_t(a, a, p0);
+                p1 = fma_t(b, b, p1);
             }
-            double err = sqrt((double)group_sum(id, pe) * (1.0 / 18.0));            // rk.py:142
-            if (err < 1.0) {                                                        // rk.py:144-155
-                factor = (err == 0.0) ? 10.0 : fmin(10.0, 0.9 * pow(err, -0.2));
-                if (rejected) factor = fmin(1.0, factor);
-            } else {                                                                // rk.py:157-159
-                accept = false;
-                factor = fmax(0.2, 0.9 * pow(err, -0.2));
+            const double m0 = (double)group_sum(id, p0) * (1.0 / 18.0);   // d0^2 (common.py:63-65 RMS norm)
+            const double m1 = (double)group_sum(id, p1) * (1.0 / 18.0);   // d1^2
+            const double interval = fabs(tf - t);
+            double h0 = (m0 < 1e-10 || m1 < 1e-10) ? 1e-6 : 0.01 * sqrt_fast(m0 * rcp_fast(m1));
+            h0 = fmin(h0, interval);
+            const T h0t = (T)h0;
+#pragma unroll
+            for (int i = 0; i < 6; ++i) Y[i] = fma_t(h0t, f[i], y[i]);   // common.py:113
+            T D1[6];
+            rhs<T>(id, sc, true, tg, Y, D1);
+            T p2 = 0;
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                const T c = (D1[i] - f[i]) * rs[i];
+                p2 = fma_t(c, c, p2);
             }
-            if (active) {
-                info.nfev += 6;
-                if (accept) {
-#pragma unroll
-                    for (int i = 0; i < 6; ++i) f[i] = k7[i];
-                }
+            const double m2 = (double)group_sum(id, p2) * (1.0 / 18.0) * rcp_fast(h0 * h0);   // d2^2
+            const double M = fmax(m1, m2);
+            // h1 = (0.01 / max(d1, d2))^(1/5) = (1e4 M)^(-1/10)
+            const double h1 = (M <= 1e-30) ? fmax(1e-6, h0 * 1e-3) : pow_m01(fmin(fmax(M * 1e4, 1e-30), 1e30));
+            if (init) {
+                h_abs = fmin(fmin(100.0 * h0, h1), interval);
+                info.nfev += 2;
             }
-        } else {
-            // classical RK4 (fixed step)
-            T k1[6], k2[6], k3[6], k4[6], Y[6];
-            rhs<T>(id, sc, y, k1);
-#pragma unroll
-            for (int i = 0; i < 6; ++i) Y[i] = fma_t(h * (T)0.5, k1[i], y[i]);
-            rhs<T>(id, sc, Y, k2);
-#pragma unroll
-            for (int i = 0; i < 6; ++i) Y[i] = fma_t(h * (T)0.5, k2[i], y[i]);
-            rhs<T>(id, sc, Y, k3);
-#pragma unroll
-            for (int i = 0; i < 6; ++i) Y[i] = fma_t(h, k3[i], y[i]);
-            rhs<T>(id, sc, Y, k4);
-#pragma unroll
-            for (int i = 0; i < 6; ++i)
-                ynew[i] = fma_t(h * (T)(1.0 / 6.0), (k1[i] + k4[i]) + (T)2 * (k2[i] + k3[i]), y[i]);
-            if (active) info.nfev += 4;
         }
 
+        // ---- one step attempt (rk.py:108-178)
+        const double min_step = min_step_of(t);
+        if (!rejected && h_abs < min_step) h_abs = min_step;
+        double t_new = t + h_abs;
+        if (t_new - tf > 0.0) t_new = tf;
+        const double h_d = t_new - t;
+        const T h = (T)h_d;
+        h_abs = fabs(h_d);                                  // rk.py:136-137: the factor scales the step actually taken
+        T k2[6], k3[6], k4[6], k5[6], k6[6], k7[6], Y[6];
+        {
+            const T c1 = h * dpc<T>(A21);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) Y[i] = fma_t(c1, f[i], y[i]);
+            rhs<T>(id, sc, true, tg, Y, k2);
+        }
+        {
+            const T c1 = h * dpc<T>(A31), c2 = h * dpc<T>(A32);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) Y[i] = fma_t(c2, k2[i], fma_t(c1, f[i], y[i]));
+            rhs<T>(id, sc, true, tg, Y, k3);
+        }
+        {
+            const T c1 = h * dpc<T>(A41), c2 = h * dpc<T>(A42), c3 = h * dpc<T>(A43);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) Y[i] = fma_t(c3, k3[i], fma_t(c2, k2[i], fma_t(c1, f[i], y[i])));
+            rhs<T>(id, sc, true, tg, Y, k4);
+        }
+        {
+            const T c1 = h * dpc<T>(A51), c2 = h * dpc<T>(A52), c3 = h * dpc<T>(A53), c4 = h * dpc<T>(A54);
+#pragma unroll
+            for (int i = 0; i < 6; ++i)
+                Y[i] = fma_t(c4, k4[i], fma_t(c3, k3[i], fma_t(c2, k2[i], fma_t(c1, f[i], y[i]))));
+            rhs<T>(id, sc, true, tg, Y, k5);
+        }
+        {
+            const T c1 = h * dpc<T>(A61), c2 = h * dpc<T>(A62), c3 = h * dpc<T>(A63), c4 = h * dpc<T>(A64),
+                    c5 = h * dpc<T>(A65);
+#pragma unroll
+            for (int i = 0; i < 6; ++i)
+                Y[i] = fma_t(c5, k5[i], fma_t(c4, k4[i], fma_t(c3, k3[i], fma_t(c2, k2[i], fma_t(c1, f[i], y[i])))));
+            rhs<T>(id, sc, true, tg, Y, k6);
+        }
+        T e5[6];   // the k1..k6 part of the error estimate (k2 has weight 0); k2..k5 die here
+        {
+            const T c1 = h * dpc<T>(B1), c3 = h * dpc<T>(B3), c4 = h * dpc<T>(B4), c5 = h * dpc<T>(B5), c6 = h * dpc<T>(B6);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                Y[i] = fma_t(c6, k6[i], fma_t(c5, k5[i], fma_t(c4, k4[i], fma_t(c3, k3[i], fma_t(c1, f[i], y[i])))));
+                e5[i] = fma_t(dpc<T>(E6), k6[i], fma_t(dpc<T>(E5), k5[i], fma_t(dpc<T>(E4), k4[i],
+                              fma_t(dpc<T>(E3), k3[i], dpc<T>(E1) * f[i]))));
+            }
+            rhs<T>(id, sc, true, tg, Y, k7);                // f(t + h, y_new)
+        }
+        // ---- error norm and step-size control (rk.py:139-159)
+        T pe = 0;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            const T e = fma_t(dpc<T>(E7), k7[i], e5[i]);
+            const T sc_i = fma_t(max_t(abs_t(y[i]), abs_t(Y[i])), rtol, atol);      // rk.py:141
+            const T q = e * rcp_t(sc_i);
+            pe = fma_t(q, q, pe);
+        }
+        const double m = (double)group_sum(id, pe) * (h_d * h_d) * (1.0 / 18.0);    // error_norm^2 (rk.py:142)
+        const bool accept = m < 1.0;                                                // rk.py:144
+        const double fac = 0.9 * pow_m01(fmin(fmax(m, 1e-14), 1e10));               // SAFETY * norm^(-1/5)
+        double factor;
+        if (accept) {
+            factor = (m == 0.0) ? 10.0 : fmin(10.0, fac);                           // rk.py:145-149
+            if (rejected) factor = fmin(1.0, factor);                               // rk.py:151-152
+        } else {
+            factor = fmax(0.2, fac);                                                // rk.py:157-158
+        }
         if (active) {
             attempts += 1;
+            info.nfev += 6;
+            h_abs *= factor;
             if (accept) {
 #pragma unroll
-                for (int i = 0; i < 6; ++i) y[i] = ynew[i];
+                for (int i = 0; i < 6; ++i) {
+                    y[i] = Y[i];
+                    f[i] = k7[i];                                                   // FSAL (rk.py:170)
+                }
                 t = t_new;
                 info.nacc += 1;
                 rejected = false;
-                if (INTEG == 0) h_abs *= factor;
-                if (INTEG == 1) steps_left -= 1;
                 if (t == tf) need_sec = true;
             } else {
-                h_abs *= factor;
                 rejected = true;
                 info.nrej += 1;
-                if (h_abs < min_step) {   // rk.py:129-130 TOO_SMALL_STEP
+                if (h_abs < min_step || !(m == m)) {   // rk.py:129-130 TOO_SMALL_STEP; NaN state (model.py:69)
                     info.failed = 1;
                     done = true;
                 }
@@ -457,7 +550,94 @@ __device__ __forceinline__ void fk_group(const LaneId& id, bool valid, const dou
                 done = true;
             }
         }
+        first = false;
     }
+}
+
+// INTEG 1: classical RK4, rk4_steps fixed steps per section (throughput mode; not the parity mode).
+template <typename T>
+__device__ __forceinline__ void fk_rk4(const LaneId& id, bool valid, const GroupScratch& gs, const double* der,
+                                       const double* alpha, int rk4_steps, T (&y)[6], FkInfo& info) {
+    const int j = id.j;
+    const int mn = (j == 2) ? 0 : j + 1, mp = (j == 0) ? 2 : j - 1;
+    initial_state<T>(j, alpha, y);
+    const int packed = valid ? gs.nsec : 0;
+    const int nsec = packed & 0xff;
+    info.nfev = info.nsec = packed >> 8;
+    info.nacc = info.nrej = info.failed = 0;
+    Section<T> sc;
+    sc.Ao = sc.Bo = sc.An = sc.Bn = sc.Ap = sc.Bp = sc.kx = sc.ky = sc.present = (T)0;
+    Trig<T> tg;
+    tg.co = tg.cp = (T)1;
+    tg.so = tg.sp = (T)0;
+    int ksec = 0, steps_left = 0;
+    double t = 0.0, tf = 0.0;
+    T h = (T)0;
+    bool done = !valid;
+    for (;;) {
+        if (__any_sync(FULL, steps_left == 0 && !done)) {
+            if (steps_left == 0 && !done) {
+                if (advance_section<T>(gs, der, nsec, j, mn, mp, ksec, done, t, tf, sc)) {
+                    h = (T)((tf - t) / (double)rk4_steps);
+                    steps_left = rk4_steps;
+                    info.nsec += 1;
+                }
+            }
+        }
+        if (!__any_sync(FULL, !done)) break;
+        const bool active = !done;
+        T Y[6], acc[6];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            Y[i] = y[i];
+            acc[i] = (T)0;
+        }
+#pragma unroll 1
+        for (int s = 0; s < 4; ++s) {
+            T D[6];
+            rhs<T>(id, sc, true, tg, Y, D);
+            const T w = (s == 0 || s == 3) ? (T)(1.0 / 6.0) : (T)(1.0 / 3.0);
+            const T c = (s == 2) ? h : h * (T)0.5;
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                acc[i] = fma_t(w, D[i], acc[i]);
+                Y[i] = fma_t(c, D[i], y[i]);
+            }
+        }
+        if (active) {
+#pragma unroll
+            for (int i = 0; i < 6; ++i) y[i] = fma_t(h, acc[i], y[i]);
+            info.nfev += 4;
+            info.nacc += 1;
+            steps_left -= 1;
+        }
+    }
+}
+
+// Per-env derived constants (domain randomisation / explicit tube parameters): C = L, Lc, EI, GJ, Ux, Uy (x3 each).
+__device__ __forceinline__ void store_derived(const double (&C)[18], GroupScratch& gs) {
+#pragma unroll
+    for (int m = 0; m < 3; ++m) {
+        const double ei = C[6 + m], gj = C[9 + m], ux = C[12 + m], uy = C[15 + m];
+        const double k = (ei != 0.0) ? ei / gj : 0.0;            // model.py:101
+        gs.der[DER_EI + m] = ei;
+        gs.der[DER_EIUX + m] = ei * ux;
+        gs.der[DER_EIUY + m] = ei * uy;
+        gs.der[DER_KX + m] = k * ux;
+        gs.der[DER_KY + m] = k * uy;
+    }
+}
+
+// beta/alpha: float64 joint values (float32 joints promoted exactly, model.py:50-61).  L / Lc: tube lengths;
+// der: the 15 derived constants of this environment's tubes (shared memory: per system, or gs.der per env).
+template <typename T, int INTEG>
+__device__ __forceinline__ void fk_group(const LaneId& id, bool valid, GroupScratch& gs, const double* L, const double* Lc,
+                                         const double* der, const double* beta, const double* alpha, double rtol_d,
+                                         double atol_d, int rk4_steps, T (&y)[6], FkInfo& info) {
+    build_sections(L, Lc, beta, gs, id.j == 0);
+    if (INTEG == 0) fk_dp45<T>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info);
+    else fk_rk4<T>(id, valid, gs, der, alpha, rk4_steps, y, info);
+    __syncwarp();   // the scratch slot may be rebuilt by the caller's next FK
 }
 
 // ---- Obs.set_action x n_substeps (obs.py:166-183, ctr_reach_env.py:134-135), float32 arithmetic -------------

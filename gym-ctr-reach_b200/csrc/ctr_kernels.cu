@@ -92,22 +92,30 @@ __device__ __forceinline__ void stage_sys(SysConst* s_sys, const SysConst* sys, 
     __syncthreads();
 }
 
-__device__ __forceinline__ void load_consts(const SysConst& sc, const double* params, int64_t n, int64_t env,
-                                            bool use_params, double (&C)[18]) {
+// Tube constants of one environment for the FK: LL = L[3], Lc[3] in registers, `der` -> the 15 derived constants in
+// shared memory (the system's, or the group's scratch slot when per-env parameters are active).
+__device__ __forceinline__ const double* env_consts(const SysConst& sc, const double* params, int64_t n, int64_t env,
+                                                    bool use_params, bool writer, GroupScratch& gs, double (&LL)[6]) {
     if (use_params) {
+        double C[18];
 #pragma unroll
         for (int i = 0; i < 18; ++i) C[i] = __ldg(params + (int64_t)i * n + env);
-    } else {
 #pragma unroll
-        for (int i = 0; i < 3; ++i) {
-            C[i] = sc.L[i];
-            C[3 + i] = sc.Lc[i];
-            C[6 + i] = sc.EI[i];
-            C[9 + i] = sc.GJ[i];
-            C[12 + i] = sc.Ux[i];
-            C[15 + i] = sc.Uy[i];
-        }
+        for (int i = 0; i < 6; ++i) LL[i] = C[i];
+        if (writer) store_derived(C, gs);
+        return gs.der;
     }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        LL[i] = sc.L[i];
+        LL[3 + i] = sc.Lc[i];
+    }
+    return sc.der;
+}
+
+constexpr int SLOTS_PER_WARP = ENVS_PER_WARP + 1;   // lanes 30 / 31 form an idle 11th group with its own scratch slot
+__device__ __forceinline__ GroupScratch& group_slot(GroupScratch* s_gs, const LaneId& id) {
+    return s_gs[(threadIdx.x >> 5) * SLOTS_PER_WARP + id.g];
 }
 
 // warp-level sum of a per-environment quantity (counted once per group: only lane j == 0 contributes)
@@ -151,6 +159,7 @@ __global__ void __launch_bounds__(BLOCK) k_fk(const SysConst* __restrict__ sys, 
                                               int rk4_steps, double* __restrict__ tip, double* __restrict__ R,
                                               int32_t* __restrict__ info_out, double* __restrict__ stats) {
     __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
+    __shared__ GroupScratch s_gs[(BLOCK / 32) * SLOTS_PER_WARP];
     stage_sys(s_sys, sys, n_systems);
     const LaneId id = lane_id();
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -159,8 +168,9 @@ __global__ void __launch_bounds__(BLOCK) k_fk(const SysConst* __restrict__ sys, 
     const int64_t e = valid ? env : 0;
     int sysid = system ? system[e] : 0;
     sysid = min(max(sysid, 0), n_systems - 1);
-    double C[18];
-    load_consts(s_sys[sysid], params, n, e, params != nullptr, C);
+    GroupScratch& gs = group_slot(s_gs, id);
+    double LL[6];
+    const double* der = env_consts(s_sys[sysid], params, n, e, params != nullptr, id.j == 0, gs, LL);
     double beta[3], alpha[3];
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
@@ -169,7 +179,7 @@ __global__ void __launch_bounds__(BLOCK) k_fk(const SysConst* __restrict__ sys, 
     }
     T y[6];
     FkInfo info;
-    fk_group<T, INTEG>(id, valid, C, C + 3, C + 6, C + 9, C + 12, C + 15, beta, alpha, rtol, atol, rk4_steps, y, info);
+    fk_group<T, INTEG>(id, valid, gs, LL, LL + 3, der, beta, alpha, rtol, atol, rk4_steps, y, info);
     if (valid) {
         tip[(int64_t)id.j * n + env] = (double)y[2];
         if (R) {
@@ -190,6 +200,7 @@ __global__ void __launch_bounds__(BLOCK) k_fk(const SysConst* __restrict__ sys, 
 template <typename T, int INTEG>
 __global__ void __launch_bounds__(BLOCK) k_step(const KArgs a, const float* __restrict__ action) {
     __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
+    __shared__ GroupScratch s_gs[(BLOCK / 32) * SLOTS_PER_WARP];
     stage_sys(s_sys, a.sys, a.n_systems);
     const LaneId id = lane_id();
     const int64_t n = a.n;
@@ -210,13 +221,14 @@ __global__ void __launch_bounds__(BLOCK) k_step(const KArgs a, const float* __re
     }
     set_action(q, act, sc, a.n_substeps);                                  // ctr_reach_env.py:134-135
 
-    double C[18];
-    load_consts(sc, p.tube_params, n, e, a.use_params != 0, C);
+    GroupScratch& gs = group_slot(s_gs, id);
+    double LL[6];
+    const double* der = env_consts(sc, p.tube_params, n, e, a.use_params != 0, j == 0, gs, LL);
     double beta[3] = {(double)q[0], (double)q[1], (double)q[2]};           // model.py:50-51
     double alpha[3] = {(double)q[3], (double)q[4], (double)q[5]};
     T y[6];
     FkInfo info;
-    fk_group<T, INTEG>(id, valid, C, C + 3, C + 6, C + 9, C + 12, C + 15, beta, alpha, a.rtol, a.atol, a.rk4_steps, y, info);
+    fk_group<T, INTEG>(id, valid, gs, LL, LL + 3, der, beta, alpha, a.rtol, a.atol, a.rk4_steps, y, info);
 
     // ---- reward / done / success / error (ctr_reach_env.py:138-140, 155-156, 168-170)
     const double ach_j = (double)y[2];
@@ -294,6 +306,7 @@ __global__ void __launch_bounds__(BLOCK) k_reset(const KArgs a, const int32_t* _
                                                  const int32_t* __restrict__ count_ptr, const double* __restrict__ goal,
                                                  const int32_t* __restrict__ system_in) {
     __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
+    __shared__ GroupScratch s_gs[(BLOCK / 32) * SLOTS_PER_WARP];
     stage_sys(s_sys, a.sys, a.n_systems);
     const LaneId id = lane_id();
     const int64_t n = a.n;
@@ -318,9 +331,13 @@ __global__ void __launch_bounds__(BLOCK) k_reset(const KArgs a, const int32_t* _
         } else sysid = 0;
         const SysConst& sc = s_sys[sysid];
 
-        double C[18];
+        GroupScratch& gs = group_slot(s_gs, id);
+        double LL[6];
+        const double* der;
+        __syncwarp();
         if (a.domain_rand > 0.0) {
             // Model.randomize_parameters (model.py:20-28, model_utils.py:5-35): U(v - v r, v + v r) on d_i, d_o, E, G, Ux
+            double C[18];
             const double* nom = a.raw_tubes + (int64_t)sysid * 24;
 #pragma unroll
             for (int tb = 0; tb < 3; ++tb) {
@@ -339,8 +356,16 @@ __global__ void __launch_bounds__(BLOCK) k_reset(const KArgs a, const int32_t* _
                 C[12 + tb] = ux;
                 C[15 + tb] = nom[tb * 8 + 7];
             }
+#pragma unroll
+            for (int i = 0; i < 6; ++i) LL[i] = C[i];
+            if (j == 0) store_derived(C, gs);
+            der = gs.der;
+            if (valid && which == 1 && p.tube_params) {
+#pragma unroll
+                for (int i = 0; i < 6; ++i) p.tube_params[(int64_t)(3 * i + j) * n + env] = pick3(j, C[3 * i], C[3 * i + 1], C[3 * i + 2]);
+            }
         } else {
-            load_consts(sc, p.tube_params, n, env, a.use_params != 0, C);
+            der = env_consts(sc, p.tube_params, n, env, a.use_params != 0, j == 0, gs, LL);
         }
 
         float q[6];
@@ -365,7 +390,7 @@ __global__ void __launch_bounds__(BLOCK) k_reset(const KArgs a, const int32_t* _
         double alpha[3] = {(double)q[3], (double)q[4], (double)q[5]};
         T y[6];
         FkInfo info;
-        fk_group<T, INTEG>(id, do_fk, C, C + 3, C + 6, C + 9, C + 12, C + 15, beta, alpha, a.rtol, a.atol, a.rk4_steps, y, info);
+        fk_group<T, INTEG>(id, do_fk, gs, LL, LL + 3, der, beta, alpha, a.rtol, a.atol, a.rk4_steps, y, info);
         double tip_j = (double)y[2];
         if (which == 0 && goal) tip_j = goal[(int64_t)j * n + env];
         const double des_j = __shfl_sync(FULL, tip_j, (id.lane + 32 - 3) & 31);   // the pair's desired-goal group
@@ -388,10 +413,6 @@ __global__ void __launch_bounds__(BLOCK) k_reset(const KArgs a, const int32_t* _
 #pragma unroll
                 for (int c = 0; c < 3; ++c) p.orientation[(int64_t)(3 * j + c) * n + env] = (double)y[3 + c];
                 write_obs(p.obs, n, env, j, q, a.rep, des_j, tip_j, tol, sysid, a.obs_dim);   // :114
-                if (a.domain_rand > 0.0 && p.tube_params) {
-#pragma unroll
-                    for (int i = 0; i < 6; ++i) p.tube_params[(int64_t)(3 * i + j) * n + env] = C[3 * i + j];
-                }
                 if (j == 0) {
                     p.t[env] = 0;                                                             // :78
                     p.system[env] = sysid;
@@ -523,6 +544,12 @@ void derive_system(const double tube[3][8], int constrain_alpha, SysConst& sc) {
         sc.high[3 + i] = constrain_alpha ? PI_F : INFINITY;
         sc.Lf[i] = (float)t[0];
         sc.slow[i] = sc.low[i];
+        const double k = (sc.EI[i] != 0.0) ? sc.EI[i] / sc.GJ[i] : 0.0;   // model.py:101
+        sc.der[DER_EI + i] = sc.EI[i];
+        sc.der[DER_EIUX + i] = sc.EI[i] * sc.Ux[i];
+        sc.der[DER_EIUY + i] = sc.EI[i] * sc.Uy[i];
+        sc.der[DER_KX + i] = k * sc.Ux[i];
+        sc.der[DER_KY + i] = k * sc.Uy[i];
     }
     sc.d10 = (float)(tube[1][0] - tube[0][0]);                       // obs.py:181 (python-float difference -> float32)
     sc.d21 = (float)(tube[2][0] - tube[1][0]);
