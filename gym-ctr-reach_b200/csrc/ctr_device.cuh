@@ -116,28 +116,41 @@ __device__ __forceinline__ double pow_m01(double x) {
 
 // sin / cos of a double with a 3-term Cody-Waite reduction (exact first product for |n| < 2^20) and the fdlibm
 // kernel polynomials on [-pi/4, pi/4]; <= 1 ulp for |x| < 1e3, <= 2 ulp up to 1e5; larger arguments take the
-// library path.  21 FP64 ops, no local memory, no call.
+// library path (out of line, so the hot loop carries only a compare and a never-taken branch).  21 FP64 ops.
+__device__ __noinline__ void sincos_slow(double x, double* s, double* c) { sincos(x, s, c); }
+
+#define TC(i, v) c_trig[i]
+__constant__ double c_trig[16] = {
+    0.63661977236758138243, 6755399441055744.0, 1.57079632673412561417e+00, 6.07710050630396597660e-11,
+    2.02226624871116645580e-21, 1.58969099521155010221e-10, -2.50507602534068634195e-08, -1.13596475577881948265e-11,
+    2.08757232129817482790e-09, 2.75573137070700676789e-06, -2.75573143513906633035e-07, -1.98412698298579493134e-04,
+    2.48015872894767294178e-05, 8.33333333332248946124e-03, -1.38888888888741095749e-03, -1.66666666666666324348e-01};
+
+// SLOW is a compile-time switch: a call inside the integration loop (even a never-taken one) makes ptxas guard every
+// shuffle group with BRA.DIV and costs 8 % of the step, so the large-argument variant is a separate instantiation
+// of the whole FK, selected once per warp (fk_group).
+template <bool SLOW>
 __device__ __forceinline__ void sincos_t(double x, double* s, double* c) {
-    if (__builtin_expect(!(fabs(x) < 1.0e5), 0)) {
-        sincos(x, s, c);
+    if (SLOW) {
+        sincos_slow(x, s, c);
         return;
     }
-    const double t = fma(x, 0.63661977236758138243, 6755399441055744.0);
+    const double t = fma(x, TC(0, 0.63661977236758138243), TC(1, 6755399441055744.0));
     const int q = __double2loint(t);
-    const double n = t - 6755399441055744.0;
-    double r = fma(-n, 1.57079632673412561417e+00, x);
-    r = fma(-n, 6.07710050630396597660e-11, r);
-    r = fma(-n, 2.02226624871116645580e-21, r);
+    const double n = t - TC(1, 6755399441055744.0);
+    double r = fma(-n, TC(2, 1.57079632673412561417e+00), x);
+    r = fma(-n, TC(3, 6.07710050630396597660e-11), r);
+    r = fma(-n, TC(4, 2.02226624871116645580e-21), r);
     const double z = r * r;
-    double ps = fma(z, 1.58969099521155010221e-10, -2.50507602534068634195e-08);
-    double pc = fma(z, -1.13596475577881948265e-11, 2.08757232129817482790e-09);
-    ps = fma(z, ps, 2.75573137070700676789e-06);
-    pc = fma(z, pc, -2.75573143513906633035e-07);
-    ps = fma(z, ps, -1.98412698298579493134e-04);
-    pc = fma(z, pc, 2.48015872894767294178e-05);
-    ps = fma(z, ps, 8.33333333332248946124e-03);
-    pc = fma(z, pc, -1.38888888888741095749e-03);
-    ps = fma(z, ps, -1.66666666666666324348e-01);
+    double ps = fma(z, TC(5, 1.58969099521155010221e-10), TC(6, -2.50507602534068634195e-08));
+    double pc = fma(z, TC(7, -1.13596475577881948265e-11), TC(8, 2.08757232129817482790e-09));
+    ps = fma(z, ps, TC(9, 2.75573137070700676789e-06));
+    pc = fma(z, pc, TC(10, -2.75573143513906633035e-07));
+    ps = fma(z, ps, TC(11, -1.98412698298579493134e-04));
+    pc = fma(z, pc, TC(12, 2.48015872894767294178e-05));
+    ps = fma(z, ps, TC(13, 8.33333333332248946124e-03));
+    pc = fma(z, pc, TC(14, -1.38888888888741095749e-03));
+    ps = fma(z, ps, TC(15, -1.66666666666666324348e-01));
     pc = fma(z, pc, 4.16666666666666019037e-02);
     double sn = fma(r * z, ps, r);
     double cs = fma(z * z, pc, fma(z, -0.5, 1.0));
@@ -153,6 +166,7 @@ __device__ __forceinline__ void sincos_t(double x, double* s, double* c) {
     *s = sn;
     *c = cs;
 }
+template <bool SLOW>
 __device__ __forceinline__ void sincos_t(float x, float* s, float* c) { sincosf(x, s, c); }
 
 // Dormand-Prince 5(4) tableau (rk.py: class RK45) in constant memory: used as c[bank][offset] operands, so the
@@ -282,12 +296,19 @@ struct Trig {
     T cp, sp;   // cos / sin(alpha_{j-1} - alpha_j)
 };
 
-template <typename T>
+// The twist integrates to a few radians at most, so the argument range of the sincos is decided once per FK from the
+// initial angle differences: true when some environment of this warp needs the library (large-argument) path.
+__device__ __forceinline__ bool needs_slow_trig(int j, const double* alpha) {
+    const double d = pick3(j, alpha[0] - alpha[1], alpha[1] - alpha[2], alpha[2] - alpha[0]);
+    return __any_sync(FULL, !(fabs(d) < 9.0e4));
+}
+
+template <typename T, bool SLOW>
 __device__ __forceinline__ void rhs(const LaneId& id, const Section<T>& sc, bool do_trig, Trig<T>& tg, const T (&Y)[6],
                                     T (&D)[6]) {
     if (do_trig) {   // warp-uniform
         const T a_next = __shfl_sync(FULL, Y[1], id.lnext);
-        sincos_t(Y[1] - a_next, &tg.so, &tg.co);
+        sincos_t<SLOW>(Y[1] - a_next, &tg.so, &tg.co);
         tg.cp = __shfl_sync(FULL, tg.co, id.lprev);
         tg.sp = __shfl_sync(FULL, tg.so, id.lprev);
     }
@@ -371,7 +392,7 @@ __device__ __forceinline__ bool advance_section(const GroupScratch& gs, const do
 
 // INTEG 0: scipy RK45 restated (rk.py rk_step/_step_impl, common.py select_initial_step), per-env adaptive.
 // On return lane j holds y = {uz_j, alpha_j, r_j, R_j0..2} at the tip.
-template <typename T>
+template <typename T, bool SLOW>
 __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const GroupScratch& gs, const double* der,
                                         const double* alpha, double rtol_d, double atol_d, T (&y)[6], FkInfo& info) {
     const int j = id.j;
@@ -415,7 +436,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
         //      whenever at least one environment starts a section (its FSAL derivative belongs to the old constants)
         if (any_init) {
             T D[6], rs[6], Y[6];
-            rhs<T>(id, sc, first, tg, y, D);                // f0 = f(t0, y0); trigonometry reused unless first
+            rhs<T, SLOW>(id, sc, first, tg, y, D);                // f0 = f(t0, y0); trigonometry reused unless first
             T p0 = 0, p1 = 0;
 #pragma unroll
             for (int i = 0; i < 6; ++i) {
@@ -434,7 +455,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(h0t, f[i], y[i]);   // common.py:113
             T D1[6];
-            rhs<T>(id, sc, true, tg, Y, D1);
+            rhs<T, SLOW>(id, sc, true, tg, Y, D1);
             T p2 = 0;
 #pragma unroll
             for (int i = 0; i < 6; ++i) {
@@ -464,26 +485,26 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
             const T c1 = h * dpc<T>(A21);
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(c1, f[i], y[i]);
-            rhs<T>(id, sc, true, tg, Y, k2);
+            rhs<T, SLOW>(id, sc, true, tg, Y, k2);
         }
         {
             const T c1 = h * dpc<T>(A31), c2 = h * dpc<T>(A32);
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(c2, k2[i], fma_t(c1, f[i], y[i]));
-            rhs<T>(id, sc, true, tg, Y, k3);
+            rhs<T, SLOW>(id, sc, true, tg, Y, k3);
         }
         {
             const T c1 = h * dpc<T>(A41), c2 = h * dpc<T>(A42), c3 = h * dpc<T>(A43);
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(c3, k3[i], fma_t(c2, k2[i], fma_t(c1, f[i], y[i])));
-            rhs<T>(id, sc, true, tg, Y, k4);
+            rhs<T, SLOW>(id, sc, true, tg, Y, k4);
         }
         {
             const T c1 = h * dpc<T>(A51), c2 = h * dpc<T>(A52), c3 = h * dpc<T>(A53), c4 = h * dpc<T>(A54);
 #pragma unroll
             for (int i = 0; i < 6; ++i)
                 Y[i] = fma_t(c4, k4[i], fma_t(c3, k3[i], fma_t(c2, k2[i], fma_t(c1, f[i], y[i]))));
-            rhs<T>(id, sc, true, tg, Y, k5);
+            rhs<T, SLOW>(id, sc, true, tg, Y, k5);
         }
         {
             const T c1 = h * dpc<T>(A61), c2 = h * dpc<T>(A62), c3 = h * dpc<T>(A63), c4 = h * dpc<T>(A64),
@@ -491,7 +512,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
 #pragma unroll
             for (int i = 0; i < 6; ++i)
                 Y[i] = fma_t(c5, k5[i], fma_t(c4, k4[i], fma_t(c3, k3[i], fma_t(c2, k2[i], fma_t(c1, f[i], y[i])))));
-            rhs<T>(id, sc, true, tg, Y, k6);
+            rhs<T, SLOW>(id, sc, true, tg, Y, k6);
         }
         T e5[6];   // the k1..k6 part of the error estimate (k2 has weight 0); k2..k5 die here
         {
@@ -502,7 +523,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
                 e5[i] = fma_t(dpc<T>(E6), k6[i], fma_t(dpc<T>(E5), k5[i], fma_t(dpc<T>(E4), k4[i],
                               fma_t(dpc<T>(E3), k3[i], dpc<T>(E1) * f[i]))));
             }
-            rhs<T>(id, sc, true, tg, Y, k7);                // f(t + h, y_new)
+            rhs<T, SLOW>(id, sc, true, tg, Y, k7);                // f(t + h, y_new)
         }
         // ---- error norm and step-size control (rk.py:139-159)
         T pe = 0;
@@ -555,7 +576,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
 }
 
 // INTEG 1: classical RK4, rk4_steps fixed steps per section (throughput mode; not the parity mode).
-template <typename T>
+template <typename T, bool SLOW>
 __device__ __forceinline__ void fk_rk4(const LaneId& id, bool valid, const GroupScratch& gs, const double* der,
                                        const double* alpha, int rk4_steps, T (&y)[6], FkInfo& info) {
     const int j = id.j;
@@ -595,7 +616,7 @@ __device__ __forceinline__ void fk_rk4(const LaneId& id, bool valid, const Group
 #pragma unroll 1
         for (int s = 0; s < 4; ++s) {
             T D[6];
-            rhs<T>(id, sc, true, tg, Y, D);
+            rhs<T, SLOW>(id, sc, true, tg, Y, D);
             const T w = (s == 0 || s == 3) ? (T)(1.0 / 6.0) : (T)(1.0 / 3.0);
             const T c = (s == 2) ? h : h * (T)0.5;
 #pragma unroll
@@ -635,8 +656,14 @@ __device__ __forceinline__ void fk_group(const LaneId& id, bool valid, GroupScra
                                          const double* der, const double* beta, const double* alpha, double rtol_d,
                                          double atol_d, int rk4_steps, T (&y)[6], FkInfo& info) {
     build_sections(L, Lc, beta, gs, id.j == 0);
-    if (INTEG == 0) fk_dp45<T>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info);
-    else fk_rk4<T>(id, valid, gs, der, alpha, rk4_steps, y, info);
+    const bool slow = sizeof(T) == 8 && needs_slow_trig(id.j, alpha);   // warp-uniform
+    if (INTEG == 0) {
+        if (slow) fk_dp45<T, true>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info);
+        else fk_dp45<T, false>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info);
+    } else {
+        if (slow) fk_rk4<T, true>(id, valid, gs, der, alpha, rk4_steps, y, info);
+        else fk_rk4<T, false>(id, valid, gs, der, alpha, rk4_steps, y, info);
+    }
     __syncwarp();   // the scratch slot may be rebuilt by the caller's next FK
 }
 

@@ -41,6 +41,10 @@ thread_local std::string g_err;
     } while (0)
 
 constexpr int BLOCK = 128;                       // 4 warps = 40 environments per block
+#ifndef CTR_MIN_BLOCKS
+#define CTR_MIN_BLOCKS 4
+#endif
+constexpr int MIN_BLOCKS = CTR_MIN_BLOCKS;       // register cap 65536 / (128 * MIN_BLOCKS): 4 -> 128 registers (measured: 4 beats 3 by 2-3 %)
 constexpr int ENVS_PER_BLOCK = (BLOCK / 32) * ENVS_PER_WARP;
 constexpr int N_STATS = 16;
 enum { ST_EPISODES = 0, ST_SUCCESSES, ST_SUM_ERROR, ST_SUM_RETURN, ST_SUM_LENGTH, ST_STEPS, ST_RESETS, ST_DRAWS,
@@ -153,7 +157,7 @@ __device__ __forceinline__ void write_obs(double* obs, int64_t n, int64_t env, i
 
 // ------------------------------------------------------------------------------------------------------------
 template <typename T, int INTEG>
-__global__ void __launch_bounds__(BLOCK) k_fk(const SysConst* __restrict__ sys, int n_systems,
+__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk(const SysConst* __restrict__ sys, int n_systems,
                                               const double* __restrict__ joints, const int32_t* __restrict__ system,
                                               const double* __restrict__ params, int64_t n, double rtol, double atol,
                                               int rk4_steps, double* __restrict__ tip, double* __restrict__ R,
@@ -198,7 +202,7 @@ __global__ void __launch_bounds__(BLOCK) k_fk(const SysConst* __restrict__ sys, 
 
 // ------------------------------------------------------------------------------------------------------------
 template <typename T, int INTEG>
-__global__ void __launch_bounds__(BLOCK) k_step(const KArgs a, const float* __restrict__ action) {
+__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_step(const KArgs a, const float* __restrict__ action) {
     __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
     __shared__ GroupScratch s_gs[(BLOCK / 32) * SLOTS_PER_WARP];
     stage_sys(s_sys, a.sys, a.n_systems);
@@ -302,7 +306,7 @@ __global__ void __launch_bounds__(BLOCK) k_step(const KArgs a, const float* __re
 // ------------------------------------------------------------------------------------------------------------
 // reset: a warp serves 5 environments; even groups compute the desired goal, odd groups the starting position.
 template <typename T, int INTEG>
-__global__ void __launch_bounds__(BLOCK) k_reset(const KArgs a, const int32_t* __restrict__ list,
+__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_reset(const KArgs a, const int32_t* __restrict__ list,
                                                  const int32_t* __restrict__ count_ptr, const double* __restrict__ goal,
                                                  const int32_t* __restrict__ system_in) {
     __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];

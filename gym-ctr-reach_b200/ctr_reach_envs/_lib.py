@@ -6,7 +6,7 @@ import os
 import numpy as np
 
 _ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_ROOT, 'libctr_b200.so')
+LIB_PATH = os.environ.get('CTR_B200_LIB') or os.path.join(_ROOT, 'libctr_b200.so')   # override: kernel-variant experiments
 
 ABI_VERSION = 1
 MAX_SYSTEMS = 8

@@ -1,4 +1,5 @@
-set -x
 python -m pytest tests -m gpu -x -q 2>&1 | tail -15
-python bench.py --steps 30 --warmup 5 --no-cpu > gpurun_out/bench_quick.json 2> gpurun_out/bench_quick.err; echo bench rc=$?
-tail -c 2500 gpurun_out/bench_quick.json; tail -5 gpurun_out/bench_quick.err
+CTR_B200_LIB=$PWD/gym-ctr-reach_b200/libctr_b200.so python scripts/kbench.py 2>&1 | tail -1
+for f in gym-ctr-reach_b200/variants/lib_*.so; do [ -f $f ] && CTR_B200_LIB=$PWD/$f python scripts/kbench.py 2>&1 | tail -1; done
+KB_PREC=f32 python scripts/kbench.py 2>&1 | tail -1
+KB_INTEG=rk4 python scripts/kbench.py 2>&1 | tail -1
