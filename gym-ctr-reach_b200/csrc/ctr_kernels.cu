@@ -2,8 +2,8 @@
 //
 // Kernels (all: 3 lanes per environment, 10 environments per warp, see ctr_device.cuh):
 //   k_fk      joints -> tip / R / info                     (Model.forward_kinematics, model.py:30-70)
-//   k_step    10 x set_action -> FK -> reward/done/success/error -> observation -> stats, appends finished
-//             envs to the reset list                       (CtrReachEnv.step, ctr_reach_env.py:124-158)
+//   k_step    10 x set_action -> FK -> reward/done/success/error -> observation -> stats -> auto-reset of the envs
+//             that finished, by their own warp             (CtrReachEnv.step, ctr_reach_env.py:124-158)
 //   k_reset   goal / start sampling (Philox) -> 2 FK -> observation   (CtrReachEnv.reset, ctr_reach_env.py:70-114)
 //   k_reward / k_relabel   HER compute_reward              (ctr_reach_env.py:160-170)
 //   k_set_action           standalone constraint op        (Obs.set_action, obs.py:166-183)
@@ -73,6 +73,19 @@ struct DevPtrs {
     double* stats;
     int32_t* reset_list;
     int32_t* reset_count;
+    // next-episode prefetch (auto-reset off the critical path, see k_step): the state reset() will produce for episode
+    // pf_episode[env], computed ahead of time by the refill queue
+    float* pf_joints;          // f32 [6][N]  starting joints
+    float* pf_desired_joints;  // f32 [6][N]
+    double* pf_desired_goal;   // f64 [3][N]
+    double* pf_start;          // f64 [3][N]  starting position
+    double* pf_orientation;    // f64 [9][N]
+    double* pf_tube_params;    // f64 [18][N] (domain randomisation only, else null)
+    int32_t* pf_system;        // i32 [N]
+    int32_t* pf_nfev;          // i32 [N]
+    uint32_t* pf_episode;      // u32 [N]  episode the slot was computed for (0 = invalid)
+    int32_t* rq_list[3];       // refill queues, rotated per step: consume / produce / zero
+    int32_t* rq_ctr;           // i32 [6]: count[3], cursor[3]
 };
 
 struct KArgs {
@@ -86,6 +99,11 @@ struct KArgs {
     uint2 key;
     int64_t env_offset;
     int64_t act_stride_field, act_stride_env;   // action element (i, env) at action[i * stride_field + env * stride_env]
+    int32_t prefetch;          // auto-reset through the prefetch slots (auto_reset && resample_joints)
+    int32_t rq_consume, rq_produce, rq_zero;    // refill-queue roles of this launch (indices into rq_list / rq_ctr)
+    int32_t rq_cap;            // capacity of each refill queue
+    int32_t refill_blocks;     // leading blocks of the k_step grid that only drain the refill queue
+    int64_t env_begin, env_count;               // env range of this launch (chunked host pipeline), whole handle by default
 };
 
 __device__ __forceinline__ void stage_sys(SysConst* s_sys, const SysConst* sys, int n_systems) {
@@ -115,6 +133,13 @@ __device__ __forceinline__ const double* env_consts(const SysConst& sc, const do
         LL[3 + i] = sc.Lc[i];
     }
     return sc.der;
+}
+
+// queue `env` for a refill of its prefetch slot (consumed at the front of the next k_step launch).  A full queue drops
+// the entry: that env then resets in place (correct, only slower).
+__device__ __forceinline__ void rq_push(const KArgs& a, int64_t env) {
+    const int slot = atomicAdd(a.p.rq_ctr + a.rq_produce, 1);
+    if (slot < a.rq_cap) a.p.rq_list[a.rq_produce][slot] = (int32_t)env;
 }
 
 constexpr int SLOTS_PER_WARP = ENVS_PER_WARP + 1;   // lanes 30 / 31 form an idle 11th group with its own scratch slot
@@ -200,7 +225,21 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk(const SysConst* __rest
     }
 }
 
+template <typename T, int INTEG>
+__device__ __forceinline__ void reset_envs(const KArgs& a, const LaneId& id, const SysConst* s_sys, GroupScratch* s_gs,
+                                           int64_t env, bool valid, const double* __restrict__ goal,
+                                           const int32_t* __restrict__ system_in, bool to_slot);
+
 // ------------------------------------------------------------------------------------------------------------
+// k_step grid = [refill_blocks leading blocks: only drain the refill queue] + [step blocks: 40 environments each].
+//
+// Auto-reset off the critical path.  A reset costs two FK solves that depend only on (seed, env, episode), not on the
+// step that ends the episode.  Doing them when the env finishes (in the same warp or in a following launch) puts one
+// FK latency (~70-100 us) behind the last wave of a 540 us kernel.  Instead every env owns a PREFETCH SLOT holding the
+// start state of its next episode; when it finishes, its lanes copy the slot (no FK) and queue the env for a refill,
+// and the refill queue of step k is drained at the FRONT of the step k+1 launch (leading blocks, then any warp that
+// runs out of step work).  A slot that is not ready (tag != episode + 1: first step of an episode, after seed()/
+// explicit resets) falls back to the in-place reset by the env's own warp; both paths give identical bits.
 template <typename T, int INTEG>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_step(const KArgs a, const float* __restrict__ action) {
     __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
@@ -208,103 +247,350 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_step(const KArgs a, const
     stage_sys(s_sys, a.sys, a.n_systems);
     const LaneId id = lane_id();
     const int64_t n = a.n;
-    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t env = warp * ENVS_PER_WARP + id.g;
-    const bool valid = (id.g < ENVS_PER_WARP) && (env < n);
-    const int64_t e = valid ? env : 0;
     const int j = id.j;
     const DevPtrs& p = a.p;
-
-    const int sysid = p.system[e];
-    const SysConst& sc = s_sys[sysid];
-    float q[6], act[6];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) {
-        q[i] = p.joints[(int64_t)i * n + e];
-        act[i] = action[(int64_t)i * a.act_stride_field + e * a.act_stride_env];
+    if (a.prefetch && blockIdx.x == 0 && threadIdx.x == 0) {   // the queue the NEXT launch produces into
+        p.rq_ctr[a.rq_zero] = 0;
+        p.rq_ctr[3 + a.rq_zero] = 0;
     }
-    set_action(q, act, sc, a.n_substeps);                                  // ctr_reach_env.py:134-135
+    unsigned pending = 0;          // group-leader lanes whose finished env must be reset in place
+    int64_t env_base = 0;          // env index of this warp's group 0
+    if ((int)blockIdx.x >= a.refill_blocks) {
+        const int64_t warp = ((int64_t)(blockIdx.x - a.refill_blocks) * blockDim.x + threadIdx.x) >> 5;
+        const int64_t local = warp * ENVS_PER_WARP + id.g;
+        const bool valid = (id.g < ENVS_PER_WARP) && (local < a.env_count);
+        env_base = a.env_begin + warp * ENVS_PER_WARP;
+        const int64_t env = a.env_begin + local;
+        const int64_t e = valid ? env : a.env_begin;
 
-    GroupScratch& gs = group_slot(s_gs, id);
-    double LL[6];
-    const double* der = env_consts(sc, p.tube_params, n, e, a.use_params != 0, j == 0, gs, LL);
-    double beta[3] = {(double)q[0], (double)q[1], (double)q[2]};           // model.py:50-51
-    double alpha[3] = {(double)q[3], (double)q[4], (double)q[5]};
-    T y[6];
-    FkInfo info;
-    fk_group<T, INTEG>(id, valid, gs, LL, LL + 3, der, beta, alpha, a.rtol, a.atol, a.rk4_steps, y, info);
-
-    // ---- reward / done / success / error (ctr_reach_env.py:138-140, 155-156, 168-170)
-    const double ach_j = (double)y[2];
-    const double des_j = p.desired_goal[(int64_t)j * n + e];
-    const double diff = __dsub_rn(ach_j, des_j);
-    const double sq = __dmul_rn(diff, diff);
-    const double s0 = __shfl_sync(FULL, sq, id.l0), s1 = __shfl_sync(FULL, sq, id.l0 + 1), s2 = __shfl_sync(FULL, sq, id.l0 + 2);
-    const double dist = __dsqrt_rn(__dadd_rn(__dadd_rn(s0, s1), s2));
-    const int t_new = p.t[e] + 1;
-    const bool far = dist > a.tol;
-    const double reward = (a.reward_mode == CTR_REWARD_DENSE) ? -dist : (far ? -1.0 : -0.0);
-    const bool done = (!far) || (t_new >= a.max_steps);
-    const bool success = dist < a.tol;
-
-    if (valid) {
-        p.joints[(int64_t)j * n + env] = pick3(j, q[0], q[1], q[2]);
-        p.joints[(int64_t)(3 + j) * n + env] = pick3(j, q[3], q[4], q[5]);
-        p.achieved[(int64_t)j * n + env] = ach_j;
+        const int sysid = p.system[e];
+        const SysConst& sc = s_sys[sysid];
+        float q[6], act[6];
 #pragma unroll
-        for (int c = 0; c < 3; ++c) p.orientation[(int64_t)(3 * j + c) * n + env] = (double)y[3 + c];
-        write_obs(p.obs, n, env, j, q, a.rep, des_j, ach_j, a.tol, sysid, a.obs_dim);
-        if (done && a.auto_reset) {
-            write_obs(p.terminal_obs, n, env, j, q, a.rep, des_j, ach_j, a.tol, sysid, a.obs_dim);
-            p.terminal_achieved[(int64_t)j * n + env] = ach_j;
+        for (int i = 0; i < 6; ++i) {
+            q[i] = p.joints[(int64_t)i * n + e];
+            act[i] = action[(int64_t)i * a.act_stride_field + e * a.act_stride_env];
         }
-        if (j == 0) {
-            p.reward[env] = reward;
-            p.done[env] = done ? 1 : 0;
-            p.success[env] = success ? 1 : 0;
-            p.error[env] = dist;
-            p.t[env] = t_new;
-            p.nfev[env] = info.nfev;
-            if (done && a.auto_reset) {
-                int slot = atomicAdd(p.reset_count, 1);
-                p.reset_list[slot] = (int32_t)env;
+        set_action(q, act, sc, a.n_substeps);                                  // ctr_reach_env.py:134-135
+
+        GroupScratch& gs = group_slot(s_gs, id);
+        double LL[6];
+        const double* der = env_consts(sc, p.tube_params, n, e, a.use_params != 0, j == 0, gs, LL);
+        double beta[3] = {(double)q[0], (double)q[1], (double)q[2]};           // model.py:50-51
+        double alpha[3] = {(double)q[3], (double)q[4], (double)q[5]};
+        T y[6];
+        FkInfo info;
+        fk_group<T, INTEG>(id, valid, gs, LL, LL + 3, der, beta, alpha, a.rtol, a.atol, a.rk4_steps, y, info);
+
+        // ---- reward / done / success / error (ctr_reach_env.py:138-140, 155-156, 168-170)
+        const double ach_j = (double)y[2];
+        const double des_j = p.desired_goal[(int64_t)j * n + e];
+        const double diff = __dsub_rn(ach_j, des_j);
+        const double sq = __dmul_rn(diff, diff);
+        const double s0 = __shfl_sync(FULL, sq, id.l0), s1 = __shfl_sync(FULL, sq, id.l0 + 1), s2 = __shfl_sync(FULL, sq, id.l0 + 2);
+        const double dist = __dsqrt_rn(__dadd_rn(__dadd_rn(s0, s1), s2));
+        const int t_new = p.t[e] + 1;
+        const bool far = dist > a.tol;
+        const double reward = (a.reward_mode == CTR_REWARD_DENSE) ? -dist : (far ? -1.0 : -0.0);
+        const bool done = (!far) || (t_new >= a.max_steps);
+        const bool success = dist < a.tol;
+        const bool finish = valid && done && a.auto_reset;
+
+        // prefetch slot ready?  (tag read by the group leader, acquire, then shared with the group)
+        unsigned episode = 0;
+        int ready_i = 0;
+        if (finish && a.prefetch && j == 0) {
+            episode = p.episode[env];
+            const uint32_t tag = *((volatile uint32_t*)(p.pf_episode + env));
+            ready_i = (tag == episode + 1u) ? 1 : 0;
+            __threadfence();
+        }
+        const bool ready = __shfl_sync(FULL, ready_i, id.l0) != 0;
+        episode = __shfl_sync(FULL, episode, id.l0);
+
+        if (valid) {
+            p.joints[(int64_t)j * n + env] = pick3(j, q[0], q[1], q[2]);
+            p.joints[(int64_t)(3 + j) * n + env] = pick3(j, q[3], q[4], q[5]);
+            p.achieved[(int64_t)j * n + env] = ach_j;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) p.orientation[(int64_t)(3 * j + c) * n + env] = (double)y[3 + c];
+            write_obs(p.obs, n, env, j, q, a.rep, des_j, ach_j, a.tol, sysid, a.obs_dim);
+            if (finish) {
+                write_obs(p.terminal_obs, n, env, j, q, a.rep, des_j, ach_j, a.tol, sysid, a.obs_dim);
+                p.terminal_achieved[(int64_t)j * n + env] = ach_j;
+            }
+            if (j == 0) {
+                p.reward[env] = reward;
+                p.done[env] = done ? 1 : 0;
+                p.success[env] = success ? 1 : 0;
+                p.error[env] = dist;
+                p.t[env] = t_new;
+                p.nfev[env] = info.nfev;
             }
         }
-    }
-    // ---- episode statistics: one atomic per warp per counter
-    const bool lead = valid && j == 0;
-    double v_ep = (lead && done) ? 1.0 : 0.0;
-    double v_su = (lead && done && success) ? 1.0 : 0.0;
-    double v_er = (lead && done) ? dist : 0.0;
-    double v_rt = lead ? reward : 0.0;
-    double v_ln = (lead && done) ? (double)t_new : 0.0;
-    double v_st = lead ? 1.0 : 0.0;
-    double v_fl = (lead && info.failed) ? 1.0 : 0.0;
-    double v_nf = lead ? (double)info.nfev : 0.0;
-    double v_at = lead ? (double)(info.nacc + info.nrej) : 0.0;
-    double v_sc = lead ? (double)info.nsec : 0.0;
-    v_nf = warp_sum(v_nf); v_at = warp_sum(v_at); v_sc = warp_sum(v_sc);
-    v_ep = warp_sum(v_ep); v_su = warp_sum(v_su); v_er = warp_sum(v_er); v_rt = warp_sum(v_rt);
-    v_ln = warp_sum(v_ln); v_st = warp_sum(v_st); v_fl = warp_sum(v_fl);
-    if (id.lane == 0) {
-        if (v_ep != 0.0) {
-            atomicAdd(p.stats + ST_EPISODES, v_ep);
-            atomicAdd(p.stats + ST_SUM_ERROR, v_er);
-            atomicAdd(p.stats + ST_SUM_LENGTH, v_ln);
-            if (v_su != 0.0) atomicAdd(p.stats + ST_SUCCESSES, v_su);
+        // ---- consume the prefetched start state of the next episode (CtrReachEnv.reset without its two FK solves)
+        if (finish && ready) {
+            float qn[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) qn[i] = __ldcg(p.pf_joints + (int64_t)i * n + env);
+            const float nb = pick3(j, qn[0], qn[1], qn[2]), na = pick3(j, qn[3], qn[4], qn[5]);
+            const double nd = __ldcg(p.pf_desired_goal + (int64_t)j * n + env);
+            const double ns = __ldcg(p.pf_start + (int64_t)j * n + env);
+            const int nsys = __ldcg(p.pf_system + env);
+            p.joints[(int64_t)j * n + env] = nb;
+            p.joints[(int64_t)(3 + j) * n + env] = na;
+            p.starting_joints[(int64_t)j * n + env] = nb;
+            p.starting_joints[(int64_t)(3 + j) * n + env] = na;
+            p.desired_joints[(int64_t)j * n + env] = __ldcg(p.pf_desired_joints + (int64_t)j * n + env);
+            p.desired_joints[(int64_t)(3 + j) * n + env] = __ldcg(p.pf_desired_joints + (int64_t)(3 + j) * n + env);
+            p.desired_goal[(int64_t)j * n + env] = nd;
+            p.starting_position[(int64_t)j * n + env] = ns;
+            p.achieved[(int64_t)j * n + env] = ns;
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+                p.orientation[(int64_t)(3 * j + c) * n + env] = __ldcg(p.pf_orientation + (int64_t)(3 * j + c) * n + env);
+            if (p.pf_tube_params) {
+#pragma unroll
+                for (int i = 0; i < 6; ++i)
+                    p.tube_params[(int64_t)(3 * i + j) * n + env] = __ldcg(p.pf_tube_params + (int64_t)(3 * i + j) * n + env);
+            }
+            write_obs(p.obs, n, env, j, qn, a.rep, nd, ns, a.tol, nsys, a.obs_dim);       // ctr_reach_env.py:114
+            if (j == 0) {
+                p.t[env] = 0;                                                             // :78
+                p.system[env] = nsys;
+                p.episode[env] = episode + 1u;
+                p.nfev[env] = __ldcg(p.pf_nfev + env);
+                atomicAdd(p.stats + ST_RESETS, 1.0);
+                rq_push(a, env);                                                          // refill for the episode after
+            }
         }
-        atomicAdd(p.stats + ST_SUM_RETURN, v_rt);
-        atomicAdd(p.stats + ST_STEPS, v_st);
-        atomicAdd(p.stats + ST_NFEV, v_nf);
-        atomicAdd(p.stats + ST_ATTEMPTS, v_at);
-        atomicAdd(p.stats + ST_SECTIONS, v_sc);
-        atomicAdd(p.stats + ST_FK_COUNT, v_st);
-        if (v_fl != 0.0) atomicAdd(p.stats + ST_FK_FAILED, v_fl);
+        pending = __ballot_sync(FULL, finish && !ready && j == 0);
+
+        // ---- episode statistics: one atomic per warp per counter
+        const bool lead = valid && j == 0;
+        double v_ep = (lead && done) ? 1.0 : 0.0;
+        double v_su = (lead && done && success) ? 1.0 : 0.0;
+        double v_er = (lead && done) ? dist : 0.0;
+        double v_rt = lead ? reward : 0.0;
+        double v_ln = (lead && done) ? (double)t_new : 0.0;
+        double v_st = lead ? 1.0 : 0.0;
+        double v_fl = (lead && info.failed) ? 1.0 : 0.0;
+        double v_nf = lead ? (double)info.nfev : 0.0;
+        double v_at = lead ? (double)(info.nacc + info.nrej) : 0.0;
+        double v_sc = lead ? (double)info.nsec : 0.0;
+        v_nf = warp_sum(v_nf); v_at = warp_sum(v_at); v_sc = warp_sum(v_sc);
+        v_ep = warp_sum(v_ep); v_su = warp_sum(v_su); v_er = warp_sum(v_er); v_rt = warp_sum(v_rt);
+        v_ln = warp_sum(v_ln); v_st = warp_sum(v_st); v_fl = warp_sum(v_fl);
+        if (id.lane == 0) {
+            if (v_ep != 0.0) {
+                atomicAdd(p.stats + ST_EPISODES, v_ep);
+                atomicAdd(p.stats + ST_SUM_ERROR, v_er);
+                atomicAdd(p.stats + ST_SUM_LENGTH, v_ln);
+                if (v_su != 0.0) atomicAdd(p.stats + ST_SUCCESSES, v_su);
+            }
+            atomicAdd(p.stats + ST_SUM_RETURN, v_rt);
+            atomicAdd(p.stats + ST_STEPS, v_st);
+            atomicAdd(p.stats + ST_NFEV, v_nf);
+            atomicAdd(p.stats + ST_ATTEMPTS, v_at);
+            atomicAdd(p.stats + ST_SECTIONS, v_sc);
+            atomicAdd(p.stats + ST_FK_COUNT, v_st);
+            if (v_fl != 0.0) atomicAdd(p.stats + ST_FK_FAILED, v_fl);
+        }
+    }
+    // ---- reset work of this warp, 5 environments at a time (group pairs, see reset_envs): first the in-place resets
+    //      of its own finished envs whose slot was not ready, then items of the refill queue until it is empty
+    if (a.auto_reset) {
+        for (;;) {                                                              // every condition is warp-uniform
+            const bool from_queue = (pending == 0);
+            const int pair = id.g >> 1;
+            bool rvalid = false;
+            int64_t renv = a.env_begin;
+            if (!from_queue) {
+                const unsigned src = __fns(pending, 0, pair + 1);               // leader lane of this pair's env
+                rvalid = (id.g < ENVS_PER_WARP) && (src != 0xffffffffu);
+                if (rvalid) renv = env_base + (int64_t)(src / GROUP);
+#pragma unroll
+                for (int k = 0; k < 5; ++k) pending &= pending - 1;
+            } else {
+                if (!a.prefetch) break;
+                int item0 = 0;
+                if (id.lane == 0) item0 = atomicAdd(p.rq_ctr + 3 + a.rq_consume, 5);
+                item0 = __shfl_sync(FULL, item0, 0);
+                const int count = min(__ldcg(p.rq_ctr + a.rq_consume), a.rq_cap);
+                if (item0 >= count) break;
+                const int item = item0 + pair;
+                rvalid = (id.g < ENVS_PER_WARP) && (item < count);
+                if (rvalid) renv = (int64_t)__ldcg(p.rq_list[a.rq_consume] + item);
+            }
+            reset_envs<T, INTEG>(a, id, s_sys, s_gs, renv, rvalid, nullptr, nullptr, from_queue);
+        }
     }
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// reset: a warp serves 5 environments; even groups compute the desired goal, odd groups the starting position.
+// reset of up to 5 environments by one warp (CtrReachEnv.reset, ctr_reach_env.py:70-114): group pair p = g >> 1 serves
+// `env` (the same value on the 6 lanes of the pair); the even group computes the desired goal, the odd group the
+// starting position, so the two FK solves of a reset run side by side.  Shared by k_reset (explicit reset / mask) and by
+// the tail of k_step (auto-reset of the environments that finished in this warp).  Results depend only on
+// (seed, global env index, episode): who executes the reset does not matter.
+template <typename T, int INTEG>
+__device__ __forceinline__ void reset_envs(const KArgs& a, const LaneId& id, const SysConst* s_sys, GroupScratch* s_gs,
+                                           int64_t env, bool valid, const double* __restrict__ goal,
+                                           const int32_t* __restrict__ system_in, bool to_slot) {
+    const DevPtrs& p = a.p;
+    const int64_t n = a.n;
+    const int j = id.j;
+    const int which = id.g & 1;        // 0: desired goal, 1: starting position
+    const uint64_t genv = (uint64_t)(a.env_offset + env);
+    const unsigned env_lo = (unsigned)genv, env_hi = (unsigned)(genv >> 32);
+    const unsigned episode = p.episode[env] + 1u;
+
+    int sysid;
+    if (system_in) sysid = min(max(system_in[env], 0), a.n_systems - 1);
+    else if (a.n_systems > 1) {                                      // ctr_reach_env.py:95 randint(n_systems)
+        uint4 r = philox4x32(make_uint4(env_lo, env_hi, episode, 2u << 16), a.key);
+        sysid = (int)(((uint64_t)r.x * (uint64_t)a.n_systems) >> 32);
+    } else sysid = 0;
+    const SysConst& sc = s_sys[sysid];
+
+    GroupScratch& gs = group_slot(s_gs, id);
+    double LL[6];
+    const double* der;
+    __syncwarp();
+    if (a.domain_rand > 0.0) {
+        // Model.randomize_parameters (model.py:20-28, model_utils.py:5-35): U(v - v r, v + v r) on d_i, d_o, E, G, Ux
+        double C[18];
+        const double* nom = a.raw_tubes + (int64_t)sysid * 24;
+#pragma unroll
+        for (int tb = 0; tb < 3; ++tb) {
+            uint4 r1 = philox4x32(make_uint4(env_lo, env_hi, episode, (3u << 16) | (unsigned)(2 * tb)), a.key);
+            uint4 r2 = philox4x32(make_uint4(env_lo, env_hi, episode, (3u << 16) | (unsigned)(2 * tb + 1)), a.key);
+            const double rr = a.domain_rand;
+            auto rnd = [rr](double v, unsigned bits) { return (v - v * rr) + ((v + v * rr) - (v - v * rr)) * u01(bits); };
+            double di = rnd(nom[tb * 8 + 2], r1.x), d_o = rnd(nom[tb * 8 + 3], r1.y);
+            double E = rnd(nom[tb * 8 + 4], r1.z), Gm = rnd(nom[tb * 8 + 5], r1.w), ux = rnd(nom[tb * 8 + 6], r2.x);
+            double do2 = d_o * d_o, di2 = di * di;
+            double d4 = do2 * do2 - di2 * di2;
+            C[tb] = nom[tb * 8 + 0];
+            C[3 + tb] = nom[tb * 8 + 1];
+            C[6 + tb] = E * ((3.141592653589793 * d4) / 64);           // Tube.py:15
+            C[9 + tb] = Gm * ((3.141592653589793 * d4) / 32);          // Tube.py:14
+            C[12 + tb] = ux;
+            C[15 + tb] = nom[tb * 8 + 7];
+        }
+#pragma unroll
+        for (int i = 0; i < 6; ++i) LL[i] = C[i];
+        if (j == 0) store_derived(C, gs);
+        der = gs.der;
+        double* tp = to_slot ? p.pf_tube_params : p.tube_params;
+        if (valid && which == 1 && tp) {
+#pragma unroll
+            for (int i = 0; i < 6; ++i) tp[(int64_t)(3 * i + j) * n + env] = pick3(j, C[3 * i], C[3 * i + 1], C[3 * i + 2]);
+        }
+    } else {
+        der = env_consts(sc, p.tube_params, n, env, a.use_params != 0, j == 0, gs, LL);
+    }
+
+    float q[6];
+    bool do_fk = valid;
+    int tries = 0;
+    bool ok = true;
+    if (which == 0) {
+        if (goal) do_fk = false;                                     // ctr_reach_env.py:102-103
+        else tries = sample_goal(sc, a.key, env_lo, env_hi, episode, 0u, q, ok);   // :100
+    } else {
+        if (a.resample_joints) tries = sample_goal(sc, a.key, env_lo, env_hi, episode, 1u, q, ok);   // :106
+        else {
+#pragma unroll
+            for (int i = 0; i < 6; ++i) q[i] = p.joints[(int64_t)i * n + env];                      // :111
+        }
+    }
+    if (!do_fk) {
+#pragma unroll
+        for (int i = 0; i < 6; ++i) q[i] = 0.f;
+    }
+    double beta[3] = {(double)q[0], (double)q[1], (double)q[2]};
+    double alpha[3] = {(double)q[3], (double)q[4], (double)q[5]};
+    T y[6];
+    FkInfo info;
+    fk_group<T, INTEG>(id, do_fk, gs, LL, LL + 3, der, beta, alpha, a.rtol, a.atol, a.rk4_steps, y, info);
+    double tip_j = (double)y[2];
+    if (which == 0 && goal) tip_j = goal[(int64_t)j * n + env];
+    const double des_j = __shfl_sync(FULL, tip_j, (id.lane + 32 - 3) & 31);   // the pair's desired-goal group
+    const double tol = a.tol;
+    if (valid && to_slot) {
+        // prefetch slot of the NEXT episode: consumed by k_step when the env finishes (same values as the live path)
+        if (which == 0) {
+            p.pf_desired_goal[(int64_t)j * n + env] = tip_j;
+            p.pf_desired_joints[(int64_t)j * n + env] = pick3(j, q[0], q[1], q[2]);
+            p.pf_desired_joints[(int64_t)(3 + j) * n + env] = pick3(j, q[3], q[4], q[5]);
+        } else {
+            p.pf_joints[(int64_t)j * n + env] = pick3(j, q[0], q[1], q[2]);
+            p.pf_joints[(int64_t)(3 + j) * n + env] = pick3(j, q[3], q[4], q[5]);
+            p.pf_start[(int64_t)j * n + env] = tip_j;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) p.pf_orientation[(int64_t)(3 * j + c) * n + env] = (double)y[3 + c];
+            if (j == 0) {
+                p.pf_system[env] = sysid;
+                p.pf_nfev[env] = info.nfev;
+            }
+        }
+    }
+    if (to_slot) {
+        // publish: data of all 6 lanes of the pair first, then the episode tag (release); a failed solve / stuck
+        // sampling leaves the slot invalid, the consumer then takes the in-place path and reports the failure
+        __threadfence();
+        const unsigned badmask = __ballot_sync(FULL, valid && (info.failed || !ok));
+        const unsigned pairmask = 0x3fu << (6 * (id.g >> 1));
+        __syncwarp();
+        if (valid && which == 1 && j == 0) {
+            volatile uint32_t* tag = p.pf_episode + env;
+            *tag = (badmask & pairmask) ? 0u : episode;
+        }
+    }
+    if (valid && !to_slot) {
+        if (which == 0) {
+            p.desired_goal[(int64_t)j * n + env] = tip_j;
+            if (!goal) {
+                p.desired_joints[(int64_t)j * n + env] = pick3(j, q[0], q[1], q[2]);
+                p.desired_joints[(int64_t)(3 + j) * n + env] = pick3(j, q[3], q[4], q[5]);
+            }
+        } else {
+            const float bj = pick3(j, q[0], q[1], q[2]), aj = pick3(j, q[3], q[4], q[5]);
+            p.joints[(int64_t)j * n + env] = bj;
+            p.joints[(int64_t)(3 + j) * n + env] = aj;
+            p.starting_joints[(int64_t)j * n + env] = bj;
+            p.starting_joints[(int64_t)(3 + j) * n + env] = aj;
+            p.starting_position[(int64_t)j * n + env] = tip_j;
+            p.achieved[(int64_t)j * n + env] = tip_j;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) p.orientation[(int64_t)(3 * j + c) * n + env] = (double)y[3 + c];
+            write_obs(p.obs, n, env, j, q, a.rep, des_j, tip_j, tol, sysid, a.obs_dim);   // :114
+            if (j == 0) {
+                p.t[env] = 0;                                                             // :78
+                p.system[env] = sysid;
+                p.episode[env] = episode;
+                p.nfev[env] = info.nfev;
+                if (a.prefetch) rq_push(a, env);           // queue the prefetch of the episode after this one
+            }
+        }
+    }
+    if (valid) {
+        if (j == 0) {
+            if (which == 1 && !to_slot) atomicAdd(p.stats + ST_RESETS, 1.0);   // slot path: counted when consumed
+            if (tries) atomicAdd(p.stats + ST_DRAWS, (double)tries);
+            if (info.failed) atomicAdd(p.stats + ST_FK_FAILED, 1.0);
+            if (!ok) atomicAdd(p.stats + ST_GOAL_STUCK, 1.0);                             // obs.py:204-205
+            if (do_fk) {
+                atomicAdd(p.stats + ST_NFEV, (double)info.nfev);
+                atomicAdd(p.stats + ST_ATTEMPTS, (double)(info.nacc + info.nrej));
+                atomicAdd(p.stats + ST_SECTIONS, (double)info.nsec);
+                atomicAdd(p.stats + ST_FK_COUNT, 1.0);
+            }
+        }
+    }
+}
+
 template <typename T, int INTEG>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_reset(const KArgs a, const int32_t* __restrict__ list,
                                                  const int32_t* __restrict__ count_ptr, const double* __restrict__ goal,
@@ -313,130 +599,13 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_reset(const KArgs a, cons
     __shared__ GroupScratch s_gs[(BLOCK / 32) * SLOTS_PER_WARP];
     stage_sys(s_sys, a.sys, a.n_systems);
     const LaneId id = lane_id();
-    const int64_t n = a.n;
-    const int64_t count = count_ptr ? (int64_t)*count_ptr : n;
+    const int64_t count = count_ptr ? (int64_t)*count_ptr : a.n;
     const int64_t warps_total = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    const DevPtrs& p = a.p;
-    const int j = id.j;
-    const int which = id.g & 1;        // 0: desired goal, 1: starting position
     for (int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; warp * 5 < count; warp += warps_total) {
         const int64_t item = warp * 5 + (id.g >> 1);
         const bool valid = (id.g < ENVS_PER_WARP) && (item < count);
         const int64_t env = valid ? (list ? (int64_t)list[item] : item) : 0;
-        const uint64_t genv = (uint64_t)(a.env_offset + env);
-        const unsigned env_lo = (unsigned)genv, env_hi = (unsigned)(genv >> 32);
-        const unsigned episode = p.episode[env] + 1u;
-
-        int sysid;
-        if (system_in) sysid = min(max(system_in[env], 0), a.n_systems - 1);
-        else if (a.n_systems > 1) {                                      // ctr_reach_env.py:95 randint(n_systems)
-            uint4 r = philox4x32(make_uint4(env_lo, env_hi, episode, 2u << 16), a.key);
-            sysid = (int)(((uint64_t)r.x * (uint64_t)a.n_systems) >> 32);
-        } else sysid = 0;
-        const SysConst& sc = s_sys[sysid];
-
-        GroupScratch& gs = group_slot(s_gs, id);
-        double LL[6];
-        const double* der;
-        __syncwarp();
-        if (a.domain_rand > 0.0) {
-            // Model.randomize_parameters (model.py:20-28, model_utils.py:5-35): U(v - v r, v + v r) on d_i, d_o, E, G, Ux
-            double C[18];
-            const double* nom = a.raw_tubes + (int64_t)sysid * 24;
-#pragma unroll
-            for (int tb = 0; tb < 3; ++tb) {
-                uint4 r1 = philox4x32(make_uint4(env_lo, env_hi, episode, (3u << 16) | (unsigned)(2 * tb)), a.key);
-                uint4 r2 = philox4x32(make_uint4(env_lo, env_hi, episode, (3u << 16) | (unsigned)(2 * tb + 1)), a.key);
-                const double rr = a.domain_rand;
-                auto rnd = [rr](double v, unsigned bits) { return (v - v * rr) + ((v + v * rr) - (v - v * rr)) * u01(bits); };
-                double di = rnd(nom[tb * 8 + 2], r1.x), d_o = rnd(nom[tb * 8 + 3], r1.y);
-                double E = rnd(nom[tb * 8 + 4], r1.z), Gm = rnd(nom[tb * 8 + 5], r1.w), ux = rnd(nom[tb * 8 + 6], r2.x);
-                double do2 = d_o * d_o, di2 = di * di;
-                double d4 = do2 * do2 - di2 * di2;
-                C[tb] = nom[tb * 8 + 0];
-                C[3 + tb] = nom[tb * 8 + 1];
-                C[6 + tb] = E * ((3.141592653589793 * d4) / 64);           // Tube.py:15
-                C[9 + tb] = Gm * ((3.141592653589793 * d4) / 32);          // Tube.py:14
-                C[12 + tb] = ux;
-                C[15 + tb] = nom[tb * 8 + 7];
-            }
-#pragma unroll
-            for (int i = 0; i < 6; ++i) LL[i] = C[i];
-            if (j == 0) store_derived(C, gs);
-            der = gs.der;
-            if (valid && which == 1 && p.tube_params) {
-#pragma unroll
-                for (int i = 0; i < 6; ++i) p.tube_params[(int64_t)(3 * i + j) * n + env] = pick3(j, C[3 * i], C[3 * i + 1], C[3 * i + 2]);
-            }
-        } else {
-            der = env_consts(sc, p.tube_params, n, env, a.use_params != 0, j == 0, gs, LL);
-        }
-
-        float q[6];
-        bool do_fk = valid;
-        int tries = 0;
-        bool ok = true;
-        if (which == 0) {
-            if (goal) do_fk = false;                                     // ctr_reach_env.py:102-103
-            else tries = sample_goal(sc, a.key, env_lo, env_hi, episode, 0u, q, ok);   // :100
-        } else {
-            if (a.resample_joints) tries = sample_goal(sc, a.key, env_lo, env_hi, episode, 1u, q, ok);   // :106
-            else {
-#pragma unroll
-                for (int i = 0; i < 6; ++i) q[i] = p.joints[(int64_t)i * n + env];                      // :111
-            }
-        }
-        if (!do_fk) {
-#pragma unroll
-            for (int i = 0; i < 6; ++i) q[i] = 0.f;
-        }
-        double beta[3] = {(double)q[0], (double)q[1], (double)q[2]};
-        double alpha[3] = {(double)q[3], (double)q[4], (double)q[5]};
-        T y[6];
-        FkInfo info;
-        fk_group<T, INTEG>(id, do_fk, gs, LL, LL + 3, der, beta, alpha, a.rtol, a.atol, a.rk4_steps, y, info);
-        double tip_j = (double)y[2];
-        if (which == 0 && goal) tip_j = goal[(int64_t)j * n + env];
-        const double des_j = __shfl_sync(FULL, tip_j, (id.lane + 32 - 3) & 31);   // the pair's desired-goal group
-        const double tol = a.tol;
-        if (valid) {
-            if (which == 0) {
-                p.desired_goal[(int64_t)j * n + env] = tip_j;
-                if (!goal) {
-                    p.desired_joints[(int64_t)j * n + env] = pick3(j, q[0], q[1], q[2]);
-                    p.desired_joints[(int64_t)(3 + j) * n + env] = pick3(j, q[3], q[4], q[5]);
-                }
-            } else {
-                const float bj = pick3(j, q[0], q[1], q[2]), aj = pick3(j, q[3], q[4], q[5]);
-                p.joints[(int64_t)j * n + env] = bj;
-                p.joints[(int64_t)(3 + j) * n + env] = aj;
-                p.starting_joints[(int64_t)j * n + env] = bj;
-                p.starting_joints[(int64_t)(3 + j) * n + env] = aj;
-                p.starting_position[(int64_t)j * n + env] = tip_j;
-                p.achieved[(int64_t)j * n + env] = tip_j;
-#pragma unroll
-                for (int c = 0; c < 3; ++c) p.orientation[(int64_t)(3 * j + c) * n + env] = (double)y[3 + c];
-                write_obs(p.obs, n, env, j, q, a.rep, des_j, tip_j, tol, sysid, a.obs_dim);   // :114
-                if (j == 0) {
-                    p.t[env] = 0;                                                             // :78
-                    p.system[env] = sysid;
-                    p.episode[env] = episode;
-                    p.nfev[env] = info.nfev;
-                }
-            }
-            if (j == 0) {
-                if (which == 1) atomicAdd(p.stats + ST_RESETS, 1.0);
-                if (tries) atomicAdd(p.stats + ST_DRAWS, (double)tries);
-                if (info.failed) atomicAdd(p.stats + ST_FK_FAILED, 1.0);
-                if (!ok) atomicAdd(p.stats + ST_GOAL_STUCK, 1.0);                             // obs.py:204-205
-                if (do_fk) {
-                    atomicAdd(p.stats + ST_NFEV, (double)info.nfev);
-                    atomicAdd(p.stats + ST_ATTEMPTS, (double)(info.nacc + info.nrej));
-                    atomicAdd(p.stats + ST_SECTIONS, (double)info.nsec);
-                    atomicAdd(p.stats + ST_FK_COUNT, 1.0);
-                }
-            }
-        }
+        reset_envs<T, INTEG>(a, id, s_sys, s_gs, env, valid, goal, system_in, false);
     }
 }
 
@@ -518,6 +687,9 @@ struct ctr_handle {
     std::vector<void*> allocs;
     cudaStream_t stream;       // used by the *_host entry points
     int use_params;
+    int prefetch;              // auto_reset && resample_joints: finished envs take their next start state from the slots
+    int64_t step_index;        // k_step launches so far: rotates the three refill queues
+    int32_t rq_cap;
     int64_t launches;
     int sm_count;
     // lazily allocated staging for host calls
@@ -585,7 +757,7 @@ KArgs make_args(const ctr_handle* h) {
     a.resample_joints = h->cfg.resample_joints;
     a.rk4_steps = h->cfg.rk4_steps;
     a.obs_dim = h->obs_dim;
-    a.use_params = h->use_params;
+    a.use_params = (h->use_params || h->cfg.domain_rand > 0.0) ? 1 : 0;   // randomised constants live in tube_params
     a.tol = h->tol;
     a.rtol = h->cfg.rtol;
     a.atol = h->cfg.atol;
@@ -594,6 +766,14 @@ KArgs make_args(const ctr_handle* h) {
     a.env_offset = h->cfg.env_offset;
     a.act_stride_field = h->n;
     a.act_stride_env = 1;
+    a.prefetch = h->prefetch;
+    a.rq_consume = (int32_t)(h->step_index % 3);
+    a.rq_produce = (int32_t)((h->step_index + 1) % 3);
+    a.rq_zero = (int32_t)((h->step_index + 2) % 3);
+    a.rq_cap = h->rq_cap;
+    a.refill_blocks = 0;
+    a.env_begin = 0;
+    a.env_count = h->n;
     return a;
 }
 
@@ -614,6 +794,7 @@ int launch_reset(ctr_handle* h, const int32_t* list, const int32_t* count_ptr, i
                  const int32_t* system, cudaStream_t st) {
     if (max_items <= 0) return 0;
     KArgs a = make_args(h);
+    a.rq_produce = a.rq_consume;            // explicit resets queue their prefetch for the next k_step launch
     int64_t warps = (max_items + 4) / 5;
     int64_t blocks = (warps + (BLOCK / 32) - 1) / (BLOCK / 32);
     // when the item count lives on the device, cap the grid (grid-stride loop inside) so that the common case of
@@ -692,6 +873,23 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     rc |= dev_alloc(h, &h->p.stats, N_STATS);
     rc |= dev_alloc(h, &h->p.reset_list, N);
     rc |= dev_alloc(h, &h->p.reset_count, 1);
+    h->prefetch = (cfg->auto_reset && cfg->resample_joints) ? 1 : 0;
+    h->step_index = 0;
+    h->rq_cap = (int32_t)(2 * N < 2000000000LL ? 2 * N : 2000000000LL);
+    h->p.pf_tube_params = nullptr;
+    if (h->prefetch) {
+        rc |= dev_alloc(h, &h->p.pf_joints, 6 * N);
+        rc |= dev_alloc(h, &h->p.pf_desired_joints, 6 * N);
+        rc |= dev_alloc(h, &h->p.pf_desired_goal, 3 * N);
+        rc |= dev_alloc(h, &h->p.pf_start, 3 * N);
+        rc |= dev_alloc(h, &h->p.pf_orientation, 9 * N);
+        if (cfg->domain_rand > 0.0) rc |= dev_alloc(h, &h->p.pf_tube_params, 18 * N);
+        rc |= dev_alloc(h, &h->p.pf_system, N);
+        rc |= dev_alloc(h, &h->p.pf_nfev, N);
+        rc |= dev_alloc(h, &h->p.pf_episode, N);
+        for (int k = 0; k < 3; ++k) rc |= dev_alloc(h, &h->p.rq_list[k], (int64_t)h->rq_cap);
+        rc |= dev_alloc(h, &h->p.rq_ctr, 6);
+    }
     if (rc) {
         std::string keep = g_err;
         ctr_destroy(h);
@@ -763,12 +961,19 @@ double ctr_get_tolerance(const ctr_handle* h) { return h ? h->tol : -1.0; }
 int ctr_seed(ctr_handle* h, uint64_t seed) {
     if (!h) CTR_FAIL("null handle");
     h->cfg.seed = seed;
+    if (h->prefetch) {                       // the prefetched episodes were drawn with the old key
+        CTR_CUDA(cudaSetDevice(h->device));
+        CTR_CUDA(cudaDeviceSynchronize());
+        CTR_CUDA(cudaMemset(h->p.pf_episode, 0, sizeof(uint32_t) * h->n));
+    }
     return 0;
 }
 
 int ctr_set_tube_params(ctr_handle* h, const double* params_dev, void* stream) {
     if (!h) CTR_FAIL("null handle");
     CTR_CUDA(cudaSetDevice(h->device));
+    if (h->prefetch)                         // the prefetched FK solves used the old constants
+        CTR_CUDA(cudaMemsetAsync(h->p.pf_episode, 0, sizeof(uint32_t) * h->n, (cudaStream_t)stream));
     if (!params_dev) {
         h->use_params = 0;
         return 0;
@@ -861,6 +1066,8 @@ int ctr_reset(ctr_handle* h, const uint8_t* mask_dev, const double* goal_dev, co
         CTR_CUDA(cudaGetLastError());
         return launch_reset(h, h->p.reset_list, h->p.reset_count, h->n, goal_dev, system_dev, st);
     }
+    // full reset: every env re-queues itself, so drop what the queue holds (keeps it within capacity)
+    if (h->prefetch) CTR_CUDA(cudaMemsetAsync(h->p.rq_ctr + (h->step_index % 3), 0, sizeof(int32_t), st));
     return launch_reset(h, nullptr, nullptr, h->n, goal_dev, system_dev, st);
 }
 
@@ -875,11 +1082,12 @@ int ctr_step_strided(ctr_handle* h, const float* action_dev, int64_t stride_fiel
     KArgs a = make_args(h);
     a.act_stride_field = stride_field;
     a.act_stride_env = stride_env;
-    if (h->cfg.auto_reset) CTR_CUDA(cudaMemsetAsync(h->p.reset_count, 0, sizeof(int32_t), st));
-    DISPATCH(k_step, h->cfg.integrator, h->cfg.precision, <<<grid_for(h->n), BLOCK, 0, st>>>(a, action_dev));
+    a.refill_blocks = h->prefetch ? h->sm_count : 0;     // drain the refill queue of the previous step first
+    DISPATCH(k_step, h->cfg.integrator, h->cfg.precision,
+             <<<grid_for(h->n) + a.refill_blocks, BLOCK, 0, st>>>(a, action_dev));
     h->launches += 1;
+    h->step_index += 1;
     CTR_CUDA(cudaGetLastError());
-    if (h->cfg.auto_reset) return launch_reset(h, h->p.reset_list, h->p.reset_count, h->n, nullptr, nullptr, st);
     return 0;
 }
 
