@@ -271,13 +271,7 @@ def gpu_arm(args):
     h_act = [torch.empty((6, N), dtype=torch.float32).pin_memory() for _ in range(4)]
     for k, t_ in enumerate(h_act):
         t_.copy_(pool[k].t())
-    out = {'observation': torch.empty((D, N), dtype=torch.float64).pin_memory().numpy(),
-           'achieved_goal': torch.empty((3, N), dtype=torch.float64).pin_memory().numpy(),
-           'desired_goal': torch.empty((3, N), dtype=torch.float64).pin_memory().numpy(),
-           'reward': torch.empty(N, dtype=torch.float64).pin_memory().numpy(),
-           'done': torch.empty(N, dtype=torch.uint8).pin_memory().numpy(),
-           'is_success': torch.empty(N, dtype=torch.uint8).pin_memory().numpy(),
-           'error': torch.empty(N, dtype=torch.float64).pin_memory().numpy()}
+    out = env.alloc_host_outputs()          # pinned; same row order as the device's result block
     h_np = [t_.numpy() for t_ in h_act]
     for i in range(3):
         env.step_host(h_np[i % 4], out)
@@ -324,7 +318,7 @@ def gpu_arm(args):
                        "l2": "flushed between timed steps (256 MiB memset outside the event pairs)",
                        "timing": "one CUDA event pair per step on the launch stream, summed; max over ranks"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
-                    "api": "CtrReachVecEnv.step_host -> ctr_step_host (pinned host buffers, synchronous)", "checksum": checksum},
+                    "api": "CtrReachVecEnv.step_host -> ctr_step_host (pinned host buffers, synchronous; chunks pipelined H2D / k_step / D2H, replayed as a CUDA graph)", "checksum": checksum},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "fma", "kernel": "k_step<%s,%s>" % (args.precision, args.integrator), "achieved": achieved,

@@ -82,7 +82,20 @@ __device__ __forceinline__ double rcp_fast(double x) {
     r = fma(r, e, r);
     return r;
 }
+// 1 / scale inside the RMS norms (rk.py:141-142, common.py:105): MUFU.RCP64H seed + ONE Newton step.  The error norm
+// only has to be exact enough that no accept / reject decision flips (|norm - 1| < error): measured seed error <= 2^-21
+// -> 2^-42 after one step, i.e. a flip probability ~1e-12 per attempt.
+__device__ __forceinline__ double rcp_1n(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    const double e = fma(-x, r, 1.0);
+    return fma(r, e, r);
+}
+#ifdef CTR_RCP1
+__device__ __forceinline__ double rcp_t(double a) { return rcp_1n(a); }
+#else
 __device__ __forceinline__ double rcp_t(double a) { return rcp_fast(a); }
+#endif
 __device__ __forceinline__ float rcp_t(float a) { return 1.0f / a; }
 
 // sqrt(x) for normal positive x (MUFU.RSQ64H seed + Goldschmidt, final residual correction)
@@ -154,6 +167,7 @@ __device__ __forceinline__ void sincos_t(double x, double* s, double* c) {
     pc = fma(z, pc, 4.16666666666666019037e-02);
     double sn = fma(r * z, ps, r);
     double cs = fma(z * z, pc, fma(z, -0.5, 1.0));
+#ifdef CTR_TRIG_FP_SIGN
     if (q & 1) {
         const double tmp = sn;
         sn = cs;
@@ -165,6 +179,16 @@ __device__ __forceinline__ void sincos_t(double x, double* s, double* c) {
     }
     *s = sn;
     *c = cs;
+#else
+    // quadrant fix-up on the integer pipe (the FP64 pipe is the bound: no DADD negations, no FP64 selects):
+    // sin = (q&1 ? cs : sn) * (-1)^(q>>1),  cos = (q&1 ? sn : cs) * (-1)^((q+1)>>1)
+    const bool swap = q & 1;
+    const int hs = __double2hiint(sn), ls = __double2loint(sn), hc = __double2hiint(cs), lc = __double2loint(cs);
+    const int s_hi = (swap ? hc : hs) ^ ((q & 2) << 30);
+    const int c_hi = (swap ? hs : hc) ^ (((q + 1) & 2) << 30);
+    *s = __hiloint2double(s_hi, swap ? lc : ls);
+    *c = __hiloint2double(c_hi, swap ? ls : lc);
+#endif
 }
 template <bool SLOW>
 __device__ __forceinline__ void sincos_t(float x, float* s, float* c) { sincosf(x, s, c); }

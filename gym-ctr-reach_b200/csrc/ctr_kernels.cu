@@ -672,6 +672,21 @@ __global__ void __launch_bounds__(256) k_fma_peak(T* out, int iters, T b, T c) {
 }  // namespace
 
 // ================================================================================================================
+constexpr int N_COMPUTE_STREAMS = 4;
+
+struct HostGraph {              // one captured ctr_step_host pipeline (keyed by the caller's host pointers)
+    const void* key[8];
+    int64_t per;
+    bool packed;
+    uint64_t stamp;
+    cudaGraph_t graph;
+    cudaGraphExec_t exec;
+    std::vector<cudaGraphNode_t> knodes;
+    std::vector<cudaKernelNodeParams> kparams;
+    std::vector<int64_t> begin, count;
+    std::vector<int32_t> refill;
+};
+
 struct ctr_handle {
     ctr_config cfg;
     int64_t n;
@@ -685,7 +700,13 @@ struct ctr_handle {
     void* fields[CTR_F_COUNT];
     int64_t field_bytes[CTR_F_COUNT];
     std::vector<void*> allocs;
-    cudaStream_t stream;       // used by the *_host entry points
+    cudaStream_t stream;       // used by the *_host entry points (= streams[0])
+    cudaStream_t streams[N_COMPUTE_STREAMS + 1];   // ctr_step_host: compute streams (chunks round-robin) + one copy-back stream
+    int host_chunks;           // chunks per ctr_step_host call (0: one per 16384 envs, at most 16); $CTR_HOST_CHUNKS
+    int host_graphs;           // replay the pipeline as a CUDA graph (default; $CTR_HOST_GRAPH=0 submits call by call)
+    cudaEvent_t ev_fork, ev_join[N_COMPUTE_STREAMS + 1], ev_chunk[16];
+    std::vector<HostGraph> graphs;
+    uint64_t graph_clock;
     int use_params;
     int prefetch;              // auto_reset && resample_joints: finished envs take their next start state from the slots
     int64_t step_index;        // k_step launches so far: rotates the three refill queues
@@ -851,21 +872,31 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     int rc = 0;
     rc |= dev_alloc(h, &h->sys_dev, CTR_MAX_SYSTEMS);
     rc |= dev_alloc(h, &h->raw_dev, CTR_MAX_SYSTEMS * 24);
+    // the per-step results live in ONE block, in the order obs | achieved | desired | reward | error (f64 rows) and
+    // done | success (u8 rows): a host caller whose arrays have the same order gets two DMA transfers per chunk
+    {
+        double* blk = nullptr;
+        uint8_t* flg = nullptr;
+        rc |= dev_alloc(h, &blk, (D + 8) * N);
+        rc |= dev_alloc(h, &flg, 2 * N);
+        if (!rc) {
+            h->p.obs = blk;
+            h->p.achieved = blk + D * N;
+            h->p.desired_goal = blk + (D + 3) * N;
+            h->p.reward = blk + (D + 6) * N;
+            h->p.error = blk + (D + 7) * N;
+            h->p.done = flg;
+            h->p.success = flg + N;
+        }
+    }
     rc |= dev_alloc(h, &h->p.joints, 6 * N);
-    rc |= dev_alloc(h, &h->p.desired_goal, 3 * N);
     rc |= dev_alloc(h, &h->p.desired_joints, 6 * N);
     rc |= dev_alloc(h, &h->p.starting_joints, 6 * N);
     rc |= dev_alloc(h, &h->p.starting_position, 3 * N);
-    rc |= dev_alloc(h, &h->p.achieved, 3 * N);
     rc |= dev_alloc(h, &h->p.orientation, 9 * N);
     rc |= dev_alloc(h, &h->p.t, N);
     rc |= dev_alloc(h, &h->p.system, N);
     rc |= dev_alloc(h, &h->p.episode, N);
-    rc |= dev_alloc(h, &h->p.obs, D * N);
-    rc |= dev_alloc(h, &h->p.reward, N);
-    rc |= dev_alloc(h, &h->p.done, N);
-    rc |= dev_alloc(h, &h->p.success, N);
-    rc |= dev_alloc(h, &h->p.error, N);
     rc |= dev_alloc(h, &h->p.terminal_obs, D * N);
     rc |= dev_alloc(h, &h->p.terminal_achieved, 3 * N);
     rc |= dev_alloc(h, &h->p.tube_params, 18 * N);
@@ -899,6 +930,16 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     CTR_CUDA(cudaMemcpy(h->sys_dev, h->sys_host.data(), sizeof(SysConst) * CTR_MAX_SYSTEMS, cudaMemcpyHostToDevice));
     CTR_CUDA(cudaMemcpy(h->raw_dev, cfg->tube, sizeof(double) * CTR_MAX_SYSTEMS * 24, cudaMemcpyHostToDevice));
     CTR_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    h->streams[0] = h->stream;
+    for (int k = 1; k <= N_COMPUTE_STREAMS; ++k) {
+        CTR_CUDA(cudaStreamCreateWithFlags(&h->streams[k], cudaStreamNonBlocking));
+        CTR_CUDA(cudaEventCreateWithFlags(&h->ev_join[k], cudaEventDisableTiming));
+    }
+    for (int k = 0; k < 16; ++k) CTR_CUDA(cudaEventCreateWithFlags(&h->ev_chunk[k], cudaEventDisableTiming));
+    h->host_chunks = getenv("CTR_HOST_CHUNKS") ? atoi(getenv("CTR_HOST_CHUNKS")) : 0;
+    h->host_graphs = getenv("CTR_HOST_GRAPH") ? atoi(getenv("CTR_HOST_GRAPH")) : 1;
+    h->graph_clock = 0;
+    CTR_CUDA(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
     void* f[CTR_F_COUNT] = {h->p.joints, h->p.desired_goal, h->p.desired_joints, h->p.starting_joints,
                             h->p.starting_position, h->p.achieved, h->p.orientation, h->p.t, h->p.system, h->p.episode,
                             h->p.obs, h->p.reward, h->p.done, h->p.success, h->p.error, h->p.terminal_obs,
@@ -922,6 +963,17 @@ int ctr_destroy(ctr_handle* h) {
     if (h->stage_fk_in) cudaFreeHost(h->stage_fk_in);
     if (h->stage_fk_dev) cudaFree(h->stage_fk_dev);
     if (h->stream) cudaStreamDestroy(h->stream);
+    for (int k = 1; k <= N_COMPUTE_STREAMS; ++k) {
+        if (h->streams[k]) cudaStreamDestroy(h->streams[k]);
+        if (h->ev_join[k]) cudaEventDestroy(h->ev_join[k]);
+    }
+    for (int k = 0; k < 16; ++k)
+        if (h->ev_chunk[k]) cudaEventDestroy(h->ev_chunk[k]);
+    for (auto& g : h->graphs) {
+        cudaGraphExecDestroy(g.exec);
+        cudaGraphDestroy(g.graph);
+    }
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     delete h;
     return 0;
 }
@@ -1075,20 +1127,29 @@ int ctr_step(ctr_handle* h, const float* action_dev, void* stream) {
     return ctr_step_strided(h, action_dev, h ? h->n : 0, 1, stream);
 }
 
+// one k_step launch over the env range [begin, begin + count)
+static int launch_step_range(ctr_handle* h, KArgs a, const float* action_dev, int64_t begin, int64_t count,
+                             int refill_blocks, cudaStream_t st) {
+    a.env_begin = begin;
+    a.env_count = count;
+    a.refill_blocks = refill_blocks;
+    DISPATCH(k_step, h->cfg.integrator, h->cfg.precision,
+             <<<grid_for(count) + refill_blocks, BLOCK, 0, st>>>(a, action_dev));
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int ctr_step_strided(ctr_handle* h, const float* action_dev, int64_t stride_field, int64_t stride_env, void* stream) {
     if (!h || !action_dev) CTR_FAIL("null argument");
     CTR_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = (cudaStream_t)stream;
     KArgs a = make_args(h);
     a.act_stride_field = stride_field;
     a.act_stride_env = stride_env;
-    a.refill_blocks = h->prefetch ? h->sm_count : 0;     // drain the refill queue of the previous step first
-    DISPATCH(k_step, h->cfg.integrator, h->cfg.precision,
-             <<<grid_for(h->n) + a.refill_blocks, BLOCK, 0, st>>>(a, action_dev));
-    h->launches += 1;
+    // leading blocks drain the refill queue of the previous step first (see k_step)
+    int rc = launch_step_range(h, a, action_dev, 0, h->n, h->prefetch ? h->sm_count : 0, (cudaStream_t)stream);
     h->step_index += 1;
-    CTR_CUDA(cudaGetLastError());
-    return 0;
+    return rc;
 }
 
 static int copy_out(ctr_handle* h, cudaStream_t st, double* obs, double* ach, double* des, double* rew, uint8_t* done,
@@ -1105,16 +1166,163 @@ static int copy_out(ctr_handle* h, cudaStream_t st, double* obs, double* ach, do
     return 0;
 }
 
+// End-to-end step with HOST buffers, pipelined: the env range is cut into chunks; chunk c runs H2D(actions) -> k_step
+// -> D2H(results) on stream c & 1, so the 170 B/env of results of one chunk cross PCIe while the next chunks compute
+// (a single launch followed by one copy left the GPU idle for the whole 22 MB transfer).  The ~9 API calls per chunk
+// cost more CPU time than the chunk takes on the GPU, so the whole sequence is captured ONCE per set of host pointers
+// into a CUDA graph; a step is then: refresh the kernel nodes' arguments (tolerance, queue roles), one graph launch.
+static int enqueue_host_step(ctr_handle* h, const KArgs& a, int64_t per, const float* action_host, double* obs_host,
+                             double* achieved_host, double* desired_host, double* reward_host, uint8_t* done_host,
+                             uint8_t* success_host, double* error_host, bool packed) {
+    const int64_t N = h->n;
+    const size_t D = (size_t)h->obs_dim;
+    // kernels alternate between two compute streams (the tail of one chunk overlaps the next chunk); all result copies
+    // go to a third stream, each waiting only for its own chunk's kernel
+    cudaStream_t s0 = h->streams[0], sc = h->streams[N_COMPUTE_STREAMS];
+    CTR_CUDA(cudaEventRecord(h->ev_fork, s0));
+    for (int k = 1; k <= N_COMPUTE_STREAMS; ++k) CTR_CUDA(cudaStreamWaitEvent(h->streams[k], h->ev_fork, 0));
+    int c = 0;
+    for (int64_t b = 0; b < N; b += per, ++c) {
+        const int64_t cnt = (N - b < per) ? N - b : per;
+        cudaStream_t sk = h->streams[c % N_COMPUTE_STREAMS];
+        CTR_CUDA(cudaMemcpy2DAsync(h->stage_action + b, sizeof(float) * N, action_host + b, sizeof(float) * N,
+                                   sizeof(float) * cnt, 6, cudaMemcpyHostToDevice, sk));
+        int rc = launch_step_range(h, a, h->stage_action, b, cnt, (c == 0 && h->prefetch) ? h->sm_count : 0, sk);
+        if (rc) return rc;
+        CTR_CUDA(cudaEventRecord(h->ev_chunk[c], sk));
+        CTR_CUDA(cudaStreamWaitEvent(sc, h->ev_chunk[c], 0));
+        cudaStream_t st = sc;
+        const size_t pitch = sizeof(double) * N, w = sizeof(double) * cnt;
+        if (packed) {
+            CTR_CUDA(cudaMemcpy2DAsync(obs_host + b, pitch, h->p.obs + b, pitch, w, D + 8, cudaMemcpyDeviceToHost, st));
+        } else {
+            if (obs_host) CTR_CUDA(cudaMemcpy2DAsync(obs_host + b, pitch, h->p.obs + b, pitch, w, D, cudaMemcpyDeviceToHost, st));
+            if (achieved_host) CTR_CUDA(cudaMemcpy2DAsync(achieved_host + b, pitch, h->p.achieved + b, pitch, w, 3, cudaMemcpyDeviceToHost, st));
+            if (desired_host) CTR_CUDA(cudaMemcpy2DAsync(desired_host + b, pitch, h->p.desired_goal + b, pitch, w, 3, cudaMemcpyDeviceToHost, st));
+            if (reward_host) CTR_CUDA(cudaMemcpyAsync(reward_host + b, h->p.reward + b, w, cudaMemcpyDeviceToHost, st));
+            if (error_host) CTR_CUDA(cudaMemcpyAsync(error_host + b, h->p.error + b, w, cudaMemcpyDeviceToHost, st));
+        }
+        if (packed) {
+            CTR_CUDA(cudaMemcpy2DAsync(done_host + b, (size_t)N, h->p.done + b, (size_t)N, (size_t)cnt, 2, cudaMemcpyDeviceToHost, st));
+        } else {
+            if (done_host) CTR_CUDA(cudaMemcpyAsync(done_host + b, h->p.done + b, cnt, cudaMemcpyDeviceToHost, st));
+            if (success_host) CTR_CUDA(cudaMemcpyAsync(success_host + b, h->p.success + b, cnt, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    for (int k = 1; k <= N_COMPUTE_STREAMS; ++k) {
+        CTR_CUDA(cudaEventRecord(h->ev_join[k], h->streams[k]));
+        CTR_CUDA(cudaStreamWaitEvent(s0, h->ev_join[k], 0));
+    }
+    return 0;
+}
+
+static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_host, double* achieved_host,
+                          double* desired_host, double* reward_host, uint8_t* done_host, uint8_t* success_host,
+                          double* error_host, bool packed);
+
 int ctr_step_host(ctr_handle* h, const float* action_host, double* obs_host, double* achieved_host, double* desired_host,
                   double* reward_host, uint8_t* done_host, uint8_t* success_host, double* error_host) {
+    return step_host_impl(h, action_host, obs_host, achieved_host, desired_host, reward_host, done_host, success_host,
+                          error_host, false);
+}
+
+int ctr_step_host_packed(ctr_handle* h, const float* action_host, double* out_f64_host, uint8_t* out_u8_host) {
+    if (!h || !out_f64_host || !out_u8_host) CTR_FAIL("null argument");
+    const int64_t N = h->n, D = h->obs_dim;
+    return step_host_impl(h, action_host, out_f64_host, out_f64_host + D * N, out_f64_host + (D + 3) * N,
+                          out_f64_host + (D + 6) * N, out_u8_host, out_u8_host + N, out_f64_host + (D + 7) * N, true);
+}
+
+static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_host, double* achieved_host,
+                          double* desired_host, double* reward_host, uint8_t* done_host, uint8_t* success_host,
+                          double* error_host, bool packed) {
     if (!h || !action_host) CTR_FAIL("null argument");
     CTR_CUDA(cudaSetDevice(h->device));
-    if (!h->stage_action) CTR_CUDA(cudaMalloc((void**)&h->stage_action, sizeof(float) * 6 * h->n));
-    cudaStream_t st = h->stream;
-    CTR_CUDA(cudaMemcpyAsync(h->stage_action, action_host, sizeof(float) * 6 * h->n, cudaMemcpyHostToDevice, st));
-    int rc = ctr_step(h, h->stage_action, st);
-    if (rc) return rc;
-    return copy_out(h, st, obs_host, achieved_host, desired_host, reward_host, done_host, success_host, error_host);
+    const int64_t N = h->n;
+    if (!h->stage_action) CTR_CUDA(cudaMalloc((void**)&h->stage_action, sizeof(float) * 6 * N));
+    int64_t chunks = h->host_chunks > 0 ? h->host_chunks : N / 16384;
+    if (chunks < 1) chunks = 1;
+    if (chunks > 16) chunks = 16;
+    int64_t per = (N + chunks - 1) / chunks;
+    per = ((per + ENVS_PER_BLOCK - 1) / ENVS_PER_BLOCK) * ENVS_PER_BLOCK;
+    const KArgs a = make_args(h);
+    cudaStream_t s0 = h->streams[0];
+    if (!h->host_graphs) {
+        int rc = enqueue_host_step(h, a, per, action_host, obs_host, achieved_host, desired_host, reward_host, done_host,
+                                   success_host, error_host, packed);
+        if (rc) return rc;
+        h->step_index += 1;
+        CTR_CUDA(cudaStreamSynchronize(s0));
+        return 0;
+    }
+    const void* key[8] = {action_host, obs_host, achieved_host, desired_host, reward_host, done_host, success_host, error_host};
+    HostGraph* g = nullptr;
+    for (auto& c : h->graphs)
+        if (c.per == per && c.packed == packed && memcmp(c.key, key, sizeof key) == 0) g = &c;
+    if (!g) {
+        if (h->graphs.size() >= 8) {                 // evict the least recently used capture
+            size_t old = 0;
+            for (size_t i = 1; i < h->graphs.size(); ++i)
+                if (h->graphs[i].stamp < h->graphs[old].stamp) old = i;
+            cudaGraphExecDestroy(h->graphs[old].exec);
+            cudaGraphDestroy(h->graphs[old].graph);
+            h->graphs.erase(h->graphs.begin() + old);
+        }
+        HostGraph ng;
+        memcpy(ng.key, key, sizeof key);
+        ng.per = per;
+        ng.packed = packed;
+        ng.stamp = 0;
+        cudaGraph_t graph = nullptr;
+        const int64_t launches0 = h->launches;
+        CTR_CUDA(cudaStreamBeginCapture(s0, cudaStreamCaptureModeThreadLocal));
+        int rc = enqueue_host_step(h, a, per, action_host, obs_host, achieved_host, desired_host, reward_host, done_host,
+                                   success_host, error_host, packed);
+        cudaError_t ce = cudaStreamEndCapture(s0, &graph);
+        h->launches = launches0;
+        if (rc) return rc;
+        if (ce != cudaSuccess) CTR_FAIL(std::string("stream capture failed: ") + cudaGetErrorString(ce));
+        size_t nn = 0;
+        CTR_CUDA(cudaGraphGetNodes(graph, nullptr, &nn));
+        std::vector<cudaGraphNode_t> nodes(nn);
+        CTR_CUDA(cudaGraphGetNodes(graph, nodes.data(), &nn));
+        for (cudaGraphNode_t nd : nodes) {
+            cudaGraphNodeType ty;
+            CTR_CUDA(cudaGraphNodeGetType(nd, &ty));
+            if (ty != cudaGraphNodeTypeKernel) continue;
+            cudaKernelNodeParams kp;
+            CTR_CUDA(cudaGraphKernelNodeGetParams(nd, &kp));
+            const KArgs* ka = (const KArgs*)kp.kernelParams[0];
+            ng.knodes.push_back(nd);
+            ng.kparams.push_back(kp);
+            ng.begin.push_back(ka->env_begin);
+            ng.count.push_back(ka->env_count);
+            ng.refill.push_back(ka->refill_blocks);
+        }
+        CTR_CUDA(cudaGraphInstantiate(&ng.exec, graph, 0));
+        ng.graph = graph;                            // kept: the node handles stay valid with it
+        h->graphs.push_back(ng);
+        g = &h->graphs.back();
+    }
+    g->stamp = ++h->graph_clock;
+    // refresh the per-step kernel arguments (goal tolerance, refill-queue roles, seed) of every chunk's k_step node
+    const float* act_dev = h->stage_action;
+    for (size_t i = 0; i < g->knodes.size(); ++i) {
+        KArgs ai = a;
+        ai.env_begin = g->begin[i];
+        ai.env_count = g->count[i];
+        ai.refill_blocks = g->refill[i];
+        void* params[2] = {&ai, (void*)&act_dev};
+        cudaKernelNodeParams kp = g->kparams[i];
+        kp.kernelParams = params;
+        kp.extra = nullptr;
+        CTR_CUDA(cudaGraphExecKernelNodeSetParams(g->exec, g->knodes[i], &kp));
+    }
+    CTR_CUDA(cudaGraphLaunch(g->exec, s0));
+    h->launches += (int64_t)g->knodes.size();
+    h->step_index += 1;
+    CTR_CUDA(cudaStreamSynchronize(s0));
+    return 0;
 }
 
 int ctr_reset_host(ctr_handle* h, double* obs_host, double* achieved_host, double* desired_host) {

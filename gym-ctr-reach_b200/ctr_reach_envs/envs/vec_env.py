@@ -290,12 +290,29 @@ class CtrReachVecEnv(object):
         _lib.check(self.lib.ctr_work_counters(self.handle, out, self._stream()))
         return dict(zip(('nfev', 'attempts', 'sections', 'fk_solves'), list(out)))
 
+    def alloc_host_outputs(self):
+        """Pinned host arrays for step_host(), laid out like the device's result block (observation | achieved_goal |
+        desired_goal | reward | error as float64 rows, done | is_success as uint8 rows) so that ctr_step_host moves
+        each chunk's results with two DMA transfers instead of seven."""
+        N, D = self.num_envs, self.obs_dim
+        blk = torch.empty((D + 8, N), dtype=torch.float64).pin_memory()
+        flg = torch.empty((2, N), dtype=torch.uint8).pin_memory()
+        b, f = blk.numpy(), flg.numpy()
+        self._host_blocks = (blk, flg)           # keep the pinned storage alive
+        self._packed_out = {'observation': b[:D], 'achieved_goal': b[D:D + 3], 'desired_goal': b[D + 3:D + 6], 'reward': b[D + 6],
+                'error': b[D + 7], 'done': f[0], 'is_success': f[1]}
+        return self._packed_out
+
     def step_host(self, action_soa, out):
         """End-to-end step with HOST buffers (ctr_step_host): action_soa float32 [6][N] numpy (ideally pinned);
         out: dict of preallocated numpy arrays among observation [D][N], achieved_goal [3][N], desired_goal [3][N],
         reward [N], done [N] u8, is_success [N] u8, error [N].  Synchronous."""
         g = lambda k: _lib.ptr(out.get(k))
         _lib.check(self.lib.ctr_set_tolerance(self.handle, float(self.goal_tolerance.get_tol())))
+        if out is getattr(self, '_packed_out', None):         # the block layout of alloc_host_outputs()
+            _lib.check(self.lib.ctr_step_host_packed(self.handle, _lib.ptr(action_soa), self._host_blocks[0].data_ptr(),
+                                                     self._host_blocks[1].data_ptr()))
+            return out
         _lib.check(self.lib.ctr_step_host(self.handle, _lib.ptr(action_soa), g('observation'), g('achieved_goal'),
                                           g('desired_goal'), g('reward'), g('done'), g('is_success'), g('error')))
         return out

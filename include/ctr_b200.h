@@ -149,6 +149,11 @@ int ctr_step_strided(ctr_handle *h, const float *action_dev, int64_t stride_fiel
  * reward f64 [N], done/success u8 [N], error f64 [N]. */
 int ctr_step_host(ctr_handle *h, const float *action_host, double *obs_host, double *achieved_host, double *desired_host,
                   double *reward_host, uint8_t *done_host, uint8_t *success_host, double *error_host);
+/* Same step, results into TWO host blocks laid out like the device's result block: out_f64 = f64 [(D + 8)][N] with rows
+ * obs (D) | achieved (3) | desired (3) | reward (1) | error (1); out_u8 = u8 [2][N] with rows done | success.  Each
+ * chunk of the pipeline then needs two DMA transfers instead of seven.  (ctr_step_host pipelines too: the env range
+ * is cut into chunks whose H2D / kernel / D2H overlap, and the sequence is replayed as a CUDA graph per pointer set.) */
+int ctr_step_host_packed(ctr_handle *h, const float *action_host, double *out_f64_host, uint8_t *out_u8_host);
 int ctr_reset_host(ctr_handle *h, double *obs_host, double *achieved_host, double *desired_host);
 
 /* CtrReachEnv.compute_reward (ctr_reach_env.py:160-170) on arbitrary batches (HER relabelling):
