@@ -8,7 +8,10 @@ SRC = os.path.join(HERE, 'csrc', 'ctr_kernels.cu')
 DEPS = [SRC, os.path.join(HERE, 'csrc', 'ctr_device.cuh'), os.path.join(HERE, '..', 'include', 'ctr_b200.h')]
 OUT = os.path.join(HERE, 'libctr_b200.so')
 NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
-FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17', '-Xcompiler', '-fPIC',
+# -fmad=false: every FMA of the kernels is an explicit fma(); implicit contraction is off so that all instantiations of the
+# FK (k_fk / k_step / k_reset, generic and U_y == 0) round identically -- a contracted `t + h_abs * factor` in one of them
+# moved tips by 1 ulp between the auto-reset and the explicit-reset path
+FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17', '-fmad=false', '-Xcompiler', '-fPIC',
          '-shared', '-cudart', 'static']
 
 

@@ -327,7 +327,9 @@ __device__ __forceinline__ bool needs_slow_trig(int j, const double* alpha) {
     return __any_sync(FULL, !(fabs(d) < 9.0e4));
 }
 
-template <typename T, bool SLOW>
+// UY0: every tube has y_curvature == 0 (all four systems of the reference, __init__.py:9-70; domain randomisation never
+// touches U_y, model_utils.py:12-20): the B terms and ky vanish -- 5 FP64 operations and 4 registers less per call.
+template <typename T, bool SLOW, bool UY0>
 __device__ __forceinline__ void rhs(const LaneId& id, const Section<T>& sc, bool do_trig, Trig<T>& tg, const T (&Y)[6],
                                     T (&D)[6]) {
     if (do_trig) {   // warp-uniform
@@ -337,15 +339,24 @@ __device__ __forceinline__ void rhs(const LaneId& id, const Section<T>& sc, bool
         tg.sp = __shfl_sync(FULL, tg.so, id.lprev);
     }
     // model.py:87-94 with cos(0) = 1, sin(0) = 0 folded; sin(alpha_j - alpha_{j-1}) = -sp
-    T ux = fma_t(sc.An, tg.co, sc.Ao);
-    T uy = fma_t(-sc.An, tg.so, sc.Bo);
-    ux = fma_t(sc.Bn, tg.so, ux);
-    uy = fma_t(sc.Bn, tg.co, uy);
-    ux = fma_t(sc.Ap, tg.cp, ux);
-    uy = fma_t(sc.Ap, tg.sp, uy);
-    ux = fma_t(-sc.Bp, tg.sp, ux);
-    uy = fma_t(sc.Bp, tg.cp, uy);
-    D[0] = fma_t(ux, sc.ky, -(uy * sc.kx));              // model.py:101  (0 when absent: kx = ky = 0)
+    T ux, uy;
+    if (UY0) {
+        ux = fma_t(sc.An, tg.co, sc.Ao);
+        uy = -sc.An * tg.so;
+        ux = fma_t(sc.Ap, tg.cp, ux);
+        uy = fma_t(sc.Ap, tg.sp, uy);
+        D[0] = -(uy * sc.kx);                                // model.py:101 with U_y = 0
+    } else {
+        ux = fma_t(sc.An, tg.co, sc.Ao);
+        uy = fma_t(-sc.An, tg.so, sc.Bo);
+        ux = fma_t(sc.Bn, tg.so, ux);
+        uy = fma_t(sc.Bn, tg.co, uy);
+        ux = fma_t(sc.Ap, tg.cp, ux);
+        uy = fma_t(sc.Ap, tg.sp, uy);
+        ux = fma_t(-sc.Bp, tg.sp, ux);
+        uy = fma_t(sc.Bp, tg.cp, uy);
+        D[0] = fma_t(ux, sc.ky, -(uy * sc.kx));              // model.py:101  (0 when absent: kx = ky = 0)
+    }
     D[1] = sc.present * Y[0];                            // model.py:99,102
     const T ux0 = __shfl_sync(FULL, ux, id.l0);
     const T uy0 = __shfl_sync(FULL, uy, id.l0);
@@ -416,7 +427,7 @@ __device__ __forceinline__ bool advance_section(const GroupScratch& gs, const do
 
 // INTEG 0: scipy RK45 restated (rk.py rk_step/_step_impl, common.py select_initial_step), per-env adaptive.
 // On return lane j holds y = {uz_j, alpha_j, r_j, R_j0..2} at the tip.
-template <typename T, bool SLOW>
+template <typename T, bool SLOW, bool UY0>
 __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const GroupScratch& gs, const double* der,
                                         const double* alpha, double rtol_d, double atol_d, T (&y)[6], FkInfo& info) {
     const int j = id.j;
@@ -460,7 +471,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
         //      whenever at least one environment starts a section (its FSAL derivative belongs to the old constants)
         if (any_init) {
             T D[6], rs[6], Y[6];
-            rhs<T, SLOW>(id, sc, first, tg, y, D);                // f0 = f(t0, y0); trigonometry reused unless first
+            rhs<T, SLOW, UY0>(id, sc, first, tg, y, D);                // f0 = f(t0, y0); trigonometry reused unless first
             T p0 = 0, p1 = 0;
 #pragma unroll
             for (int i = 0; i < 6; ++i) {
@@ -479,7 +490,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(h0t, f[i], y[i]);   // common.py:113
             T D1[6];
-            rhs<T, SLOW>(id, sc, true, tg, Y, D1);
+            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, D1);
             T p2 = 0;
 #pragma unroll
             for (int i = 0; i < 6; ++i) {
@@ -509,26 +520,26 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
             const T c1 = h * dpc<T>(A21);
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(c1, f[i], y[i]);
-            rhs<T, SLOW>(id, sc, true, tg, Y, k2);
+            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, k2);
         }
         {
             const T c1 = h * dpc<T>(A31), c2 = h * dpc<T>(A32);
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(c2, k2[i], fma_t(c1, f[i], y[i]));
-            rhs<T, SLOW>(id, sc, true, tg, Y, k3);
+            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, k3);
         }
         {
             const T c1 = h * dpc<T>(A41), c2 = h * dpc<T>(A42), c3 = h * dpc<T>(A43);
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(c3, k3[i], fma_t(c2, k2[i], fma_t(c1, f[i], y[i])));
-            rhs<T, SLOW>(id, sc, true, tg, Y, k4);
+            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, k4);
         }
         {
             const T c1 = h * dpc<T>(A51), c2 = h * dpc<T>(A52), c3 = h * dpc<T>(A53), c4 = h * dpc<T>(A54);
 #pragma unroll
             for (int i = 0; i < 6; ++i)
                 Y[i] = fma_t(c4, k4[i], fma_t(c3, k3[i], fma_t(c2, k2[i], fma_t(c1, f[i], y[i]))));
-            rhs<T, SLOW>(id, sc, true, tg, Y, k5);
+            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, k5);
         }
         {
             const T c1 = h * dpc<T>(A61), c2 = h * dpc<T>(A62), c3 = h * dpc<T>(A63), c4 = h * dpc<T>(A64),
@@ -536,7 +547,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
 #pragma unroll
             for (int i = 0; i < 6; ++i)
                 Y[i] = fma_t(c5, k5[i], fma_t(c4, k4[i], fma_t(c3, k3[i], fma_t(c2, k2[i], fma_t(c1, f[i], y[i])))));
-            rhs<T, SLOW>(id, sc, true, tg, Y, k6);
+            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, k6);
         }
         T e5[6];   // the k1..k6 part of the error estimate (k2 has weight 0); k2..k5 die here
         {
@@ -547,7 +558,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
                 e5[i] = fma_t(dpc<T>(E6), k6[i], fma_t(dpc<T>(E5), k5[i], fma_t(dpc<T>(E4), k4[i],
                               fma_t(dpc<T>(E3), k3[i], dpc<T>(E1) * f[i]))));
             }
-            rhs<T, SLOW>(id, sc, true, tg, Y, k7);                // f(t + h, y_new)
+            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, k7);                // f(t + h, y_new)
         }
         // ---- error norm and step-size control (rk.py:139-159)
         T pe = 0;
@@ -600,7 +611,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
 }
 
 // INTEG 1: classical RK4, rk4_steps fixed steps per section (throughput mode; not the parity mode).
-template <typename T, bool SLOW>
+template <typename T, bool SLOW, bool UY0>
 __device__ __forceinline__ void fk_rk4(const LaneId& id, bool valid, const GroupScratch& gs, const double* der,
                                        const double* alpha, int rk4_steps, T (&y)[6], FkInfo& info) {
     const int j = id.j;
@@ -640,7 +651,7 @@ __device__ __forceinline__ void fk_rk4(const LaneId& id, bool valid, const Group
 #pragma unroll 1
         for (int s = 0; s < 4; ++s) {
             T D[6];
-            rhs<T, SLOW>(id, sc, true, tg, Y, D);
+            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, D);
             const T w = (s == 0 || s == 3) ? (T)(1.0 / 6.0) : (T)(1.0 / 3.0);
             const T c = (s == 2) ? h : h * (T)0.5;
 #pragma unroll
@@ -681,12 +692,13 @@ __device__ __forceinline__ void fk_group(const LaneId& id, bool valid, GroupScra
                                          double atol_d, int rk4_steps, T (&y)[6], FkInfo& info) {
     build_sections(L, Lc, beta, gs, id.j == 0);
     const bool slow = sizeof(T) == 8 && needs_slow_trig(id.j, alpha);   // warp-uniform
-    if (INTEG == 0) {
-        if (slow) fk_dp45<T, true>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info);
-        else fk_dp45<T, false>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info);
+    constexpr bool UY0 = (INTEG & 2) != 0;     // INTEG: bit 0 = integrator (0 dp45, 1 rk4), bit 1 = all U_y are zero
+    if ((INTEG & 1) == 0) {
+        if (slow) fk_dp45<T, true, UY0>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info);
+        else fk_dp45<T, false, UY0>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info);
     } else {
-        if (slow) fk_rk4<T, true>(id, valid, gs, der, alpha, rk4_steps, y, info);
-        else fk_rk4<T, false>(id, valid, gs, der, alpha, rk4_steps, y, info);
+        if (slow) fk_rk4<T, true, UY0>(id, valid, gs, der, alpha, rk4_steps, y, info);
+        else fk_rk4<T, false, UY0>(id, valid, gs, der, alpha, rk4_steps, y, info);
     }
     __syncwarp();   // the scratch slot may be rebuilt by the caller's next FK
 }

@@ -708,6 +708,7 @@ struct ctr_handle {
     std::vector<HostGraph> graphs;
     uint64_t graph_clock;
     int use_params;
+    int all_uy_zero;           // every tube of every selected system has y_curvature == 0
     int prefetch;              // auto_reset && resample_joints: finished envs take their next start state from the slots
     int64_t step_index;        // k_step launches so far: rotates the three refill queues
     int32_t rq_cap;
@@ -800,6 +801,23 @@ KArgs make_args(const ctr_handle* h) {
 
 inline int grid_for(int64_t n_envs) { return (int)((n_envs + ENVS_PER_BLOCK - 1) / ENVS_PER_BLOCK); }
 
+// k_step additionally specialises on "every tube has y_curvature == 0" (template INTEG bit 1, see rhs)
+#define DISPATCH_STEP(uy0, integ, prec, ...)                                         \
+    do {                                                                             \
+        const int sel__ = ((integ) == CTR_INTEGRATOR_DP45 ? 0 : 1) | ((uy0) ? 2 : 0); \
+        if ((prec) == CTR_PRECISION_F64) {                                           \
+            if (sel__ == 0) k_step<double, 0> __VA_ARGS__;                           \
+            else if (sel__ == 1) k_step<double, 1> __VA_ARGS__;                      \
+            else if (sel__ == 2) k_step<double, 2> __VA_ARGS__;                      \
+            else k_step<double, 3> __VA_ARGS__;                                      \
+        } else {                                                                     \
+            if (sel__ == 0) k_step<float, 0> __VA_ARGS__;                            \
+            else if (sel__ == 1) k_step<float, 1> __VA_ARGS__;                       \
+            else if (sel__ == 2) k_step<float, 2> __VA_ARGS__;                       \
+            else k_step<float, 3> __VA_ARGS__;                                       \
+        }                                                                            \
+    } while (0)
+
 #define DISPATCH(KERNEL, integ, prec, ...)                                           \
     do {                                                                             \
         if ((prec) == CTR_PRECISION_F64) {                                           \
@@ -868,6 +886,10 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     h->sys_host.resize(CTR_MAX_SYSTEMS);
     memset(h->sys_host.data(), 0, sizeof(SysConst) * CTR_MAX_SYSTEMS);
     for (int s = 0; s < cfg->n_systems; ++s) derive_system(cfg->tube[s], cfg->constrain_alpha, h->sys_host[s]);
+    h->all_uy_zero = 1;
+    for (int s = 0; s < cfg->n_systems; ++s)
+        for (int i = 0; i < 3; ++i)
+            if (cfg->tube[s][i][7] != 0.0) h->all_uy_zero = 0;
     const int64_t N = n_envs, D = h->obs_dim;
     int rc = 0;
     rc |= dev_alloc(h, &h->sys_dev, CTR_MAX_SYSTEMS);
@@ -1133,8 +1155,10 @@ static int launch_step_range(ctr_handle* h, KArgs a, const float* action_dev, in
     a.env_begin = begin;
     a.env_count = count;
     a.refill_blocks = refill_blocks;
-    DISPATCH(k_step, h->cfg.integrator, h->cfg.precision,
-             <<<grid_for(count) + refill_blocks, BLOCK, 0, st>>>(a, action_dev));
+    // U_y == 0 fast path: nominal tubes only (explicit per-env constants may carry any U_y)
+    const bool uy0 = h->all_uy_zero && !h->use_params && !getenv("CTR_NO_UY0");
+    DISPATCH_STEP(uy0, h->cfg.integrator, h->cfg.precision,
+                  <<<grid_for(count) + refill_blocks, BLOCK, 0, st>>>(a, action_dev));
     h->launches += 1;
     CTR_CUDA(cudaGetLastError());
     return 0;
