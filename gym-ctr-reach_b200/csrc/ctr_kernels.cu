@@ -40,12 +40,16 @@ thread_local std::string g_err;
         }                                                                       \
     } while (0)
 
-constexpr int BLOCK = 128;                       // 4 warps = 40 environments per block
-#ifndef CTR_MIN_BLOCKS
-#define CTR_MIN_BLOCKS 4
+#ifndef CTR_BLOCK
+#define CTR_BLOCK 128
 #endif
-constexpr int MIN_BLOCKS = CTR_MIN_BLOCKS;       // register cap 65536 / (128 * MIN_BLOCKS): 4 -> 128 registers (measured: 4 beats 3 by 2-3 %)
+constexpr int BLOCK = CTR_BLOCK;                 // 4 warps = 40 environments per block
+#ifndef CTR_MIN_BLOCKS
+#define CTR_MIN_BLOCKS (512 / CTR_BLOCK)
+#endif
+constexpr int MIN_BLOCKS = CTR_MIN_BLOCKS;       // 16 warps / SM: register cap 65536 / 512 = 128 (measured: 12 and 20 warps / SM are slower)
 constexpr int ENVS_PER_BLOCK = (BLOCK / 32) * ENVS_PER_WARP;
+constexpr int SORT_WINDOW = 640;                 // slots per sorting window (16 blocks); launches start on window boundaries
 constexpr int N_STATS = 16;
 enum { ST_EPISODES = 0, ST_SUCCESSES, ST_SUM_ERROR, ST_SUM_RETURN, ST_SUM_LENGTH, ST_STEPS, ST_RESETS, ST_DRAWS,
        ST_FK_FAILED, ST_GOAL_STUCK, ST_NFEV, ST_ATTEMPTS, ST_SECTIONS, ST_FK_COUNT };
@@ -104,6 +108,8 @@ struct KArgs {
     int32_t rq_cap;            // capacity of each refill queue
     int32_t refill_blocks;     // leading blocks of the k_step grid that only drain the refill queue
     int64_t env_begin, env_count;               // env range of this launch (chunked host pipeline), whole handle by default
+    int32_t* perm;             // slot -> env, sorted by last step's work inside windows of SORT_WINDOW slots (null: identity)
+    int32_t* win_count;        // per-window arrival counters of the blocks (self-resetting)
 };
 
 __device__ __forceinline__ void stage_sys(SysConst* s_sys, const SysConst* sys, int n_systems) {
@@ -254,13 +260,17 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_step(const KArgs a, const
         p.rq_ctr[3 + a.rq_zero] = 0;
     }
     unsigned pending = 0;          // group-leader lanes whose finished env must be reset in place
-    int64_t env_base = 0;          // env index of this warp's group 0
+    int env32 = 0;                 // env index served by this lane's group
     if ((int)blockIdx.x >= a.refill_blocks) {
         const int64_t warp = ((int64_t)(blockIdx.x - a.refill_blocks) * blockDim.x + threadIdx.x) >> 5;
         const int64_t local = warp * ENVS_PER_WARP + id.g;
         const bool valid = (id.g < ENVS_PER_WARP) && (local < a.env_count);
-        env_base = a.env_begin + warp * ENVS_PER_WARP;
-        const int64_t env = a.env_begin + local;
+        // Work-sorted assignment: slot -> env through `perm`, which the previous step sorted by each env's RHS count
+        // inside windows of 640 slots.  The 10 environments of a warp then need about the same number of step attempts
+        // and start their sections together; a warp costs max-over-its-envs, so this removes ~10 % of the lock-step
+        // waste.  Results do not depend on the assignment (every env is computed independently of its neighbours).
+        const int64_t env = (valid && a.perm) ? (int64_t)a.perm[a.env_begin + local] : a.env_begin + local;
+        env32 = (int)env;
         const int64_t e = valid ? env : a.env_begin;
 
         const int sysid = p.system[e];
@@ -366,6 +376,70 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_step(const KArgs a, const
         }
         pending = __ballot_sync(FULL, finish && !ready && j == 0);
 
+        // ---- re-sort this window for the next step: the last of its blocks to arrive does a counting sort on nfev
+        if (a.perm) {
+            __shared__ int s_hist[256];
+            __shared__ int s_last;
+            const int64_t blk = (int64_t)(blockIdx.x - a.refill_blocks);
+            constexpr int BLOCKS_PER_WINDOW = SORT_WINDOW / ENVS_PER_BLOCK;
+            const int64_t win_local = blk / BLOCKS_PER_WINDOW;
+            const int64_t slot0 = win_local * SORT_WINDOW;                           // first slot of the window, launch-relative
+            const int64_t win = (a.env_begin + slot0) / SORT_WINDOW;
+            const int nslots = (int)((a.env_count - slot0 < SORT_WINDOW) ? a.env_count - slot0 : SORT_WINDOW);
+            const int nblocks = (nslots + ENVS_PER_BLOCK - 1) / ENVS_PER_BLOCK;
+            __threadfence();
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                const int ticket = atomicAdd(a.win_count + win, 1);
+                s_last = (ticket == nblocks - 1);
+                if (s_last) a.win_count[win] = 0;
+            }
+            for (int i = threadIdx.x; i < 256; i += BLOCK) s_hist[i] = 0;
+            __syncthreads();
+            if (s_last) {                                                            // block-uniform
+                __threadfence();
+                const int64_t gbase = a.env_begin + slot0;                           // window = envs [gbase, gbase + nslots)
+                constexpr int PER = (SORT_WINDOW + BLOCK - 1) / BLOCK;
+                int bin[PER], rank[PER];
+#pragma unroll
+                for (int k = 0; k < PER; ++k) {
+                    const int i = threadIdx.x + k * BLOCK;
+                    bin[k] = -1;
+                    if (i < nslots) {
+                        bin[k] = min(max(__ldcg(p.nfev + gbase + i), 0), 255);
+                        rank[k] = atomicAdd(&s_hist[bin[k]], 1);
+                    }
+                }
+                __syncthreads();
+                if (threadIdx.x < 32) {                                              // exclusive scan of the 256 bins
+                    int v[8], sum = 0;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        v[k] = s_hist[threadIdx.x * 8 + k];
+                        sum += v[k];
+                    }
+                    int incl = sum;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int t = __shfl_up_sync(FULL, incl, o);
+                        if ((int)threadIdx.x >= o) incl += t;
+                    }
+                    int run = incl - sum;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        s_hist[threadIdx.x * 8 + k] = run;
+                        run += v[k];
+                    }
+                }
+                __syncthreads();
+#pragma unroll
+                for (int k = 0; k < PER; ++k) {
+                    const int i = threadIdx.x + k * BLOCK;
+                    if (bin[k] >= 0) a.perm[gbase + s_hist[bin[k]] + rank[k]] = (int32_t)(gbase + i);
+                }
+            }
+        }
+
         // ---- episode statistics: one atomic per warp per counter
         const bool lead = valid && j == 0;
         double v_ep = (lead && done) ? 1.0 : 0.0;
@@ -408,7 +482,8 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_step(const KArgs a, const
             if (!from_queue) {
                 const unsigned src = __fns(pending, 0, pair + 1);               // leader lane of this pair's env
                 rvalid = (id.g < ENVS_PER_WARP) && (src != 0xffffffffu);
-                if (rvalid) renv = env_base + (int64_t)(src / GROUP);
+                const int e32 = __shfl_sync(FULL, env32, src & 31);
+                if (rvalid) renv = (int64_t)e32;
 #pragma unroll
                 for (int k = 0; k < 5; ++k) pending &= pending - 1;
             } else {
@@ -708,6 +783,8 @@ struct ctr_handle {
     std::vector<HostGraph> graphs;
     uint64_t graph_clock;
     int use_params;
+    int32_t* perm;             // work-sorted slot -> env map of k_step (null: disabled)
+    int32_t* win_count;
     int all_uy_zero;           // every tube of every selected system has y_curvature == 0
     int prefetch;              // auto_reset && resample_joints: finished envs take their next start state from the slots
     int64_t step_index;        // k_step launches so far: rotates the three refill queues
@@ -796,6 +873,8 @@ KArgs make_args(const ctr_handle* h) {
     a.refill_blocks = 0;
     a.env_begin = 0;
     a.env_count = h->n;
+    a.perm = h->perm;
+    a.win_count = h->win_count;
     return a;
 }
 
@@ -926,6 +1005,17 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     rc |= dev_alloc(h, &h->p.stats, N_STATS);
     rc |= dev_alloc(h, &h->p.reset_list, N);
     rc |= dev_alloc(h, &h->p.reset_count, 1);
+    h->perm = nullptr;
+    h->win_count = nullptr;
+    if (cfg->integrator == CTR_INTEGRATOR_DP45 && !getenv("CTR_NO_SORT")) {   // fixed-step RK4 has nothing to balance
+        rc |= dev_alloc(h, &h->perm, N);
+        rc |= dev_alloc(h, &h->win_count, (N + SORT_WINDOW - 1) / SORT_WINDOW);
+        if (!rc) {
+            std::vector<int32_t> ident((size_t)N);
+            for (int64_t i = 0; i < N; ++i) ident[(size_t)i] = (int32_t)i;
+            CTR_CUDA(cudaMemcpy(h->perm, ident.data(), sizeof(int32_t) * N, cudaMemcpyHostToDevice));
+        }
+    }
     h->prefetch = (cfg->auto_reset && cfg->resample_joints) ? 1 : 0;
     h->step_index = 0;
     h->rq_cap = (int32_t)(2 * N < 2000000000LL ? 2 * N : 2000000000LL);
@@ -1268,7 +1358,7 @@ static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_h
     if (chunks < 1) chunks = 1;
     if (chunks > 16) chunks = 16;
     int64_t per = (N + chunks - 1) / chunks;
-    per = ((per + ENVS_PER_BLOCK - 1) / ENVS_PER_BLOCK) * ENVS_PER_BLOCK;
+    per = ((per + SORT_WINDOW - 1) / SORT_WINDOW) * SORT_WINDOW;      // chunks start on sorting-window boundaries
     const KArgs a = make_args(h);
     cudaStream_t s0 = h->streams[0];
     if (!h->host_graphs) {
