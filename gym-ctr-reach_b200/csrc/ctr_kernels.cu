@@ -49,7 +49,10 @@ constexpr int BLOCK = CTR_BLOCK;                 // 4 warps = 40 environments pe
 #endif
 constexpr int MIN_BLOCKS = CTR_MIN_BLOCKS;       // 16 warps / SM: register cap 65536 / 512 = 128 (measured: 12 and 20 warps / SM are slower)
 constexpr int ENVS_PER_BLOCK = (BLOCK / 32) * ENVS_PER_WARP;
-constexpr int SORT_WINDOW = 640;                 // slots per sorting window (16 blocks); launches start on window boundaries
+#ifndef CTR_SORT_WINDOW
+#define CTR_SORT_WINDOW 640
+#endif
+constexpr int SORT_WINDOW = CTR_SORT_WINDOW;                 // slots per sorting window (16 blocks); launches start on window boundaries
 constexpr int N_STATS = 16;
 enum { ST_EPISODES = 0, ST_SUCCESSES, ST_SUM_ERROR, ST_SUM_RETURN, ST_SUM_LENGTH, ST_STEPS, ST_RESETS, ST_DRAWS,
        ST_FK_FAILED, ST_GOAL_STUCK, ST_NFEV, ST_ATTEMPTS, ST_SECTIONS, ST_FK_COUNT };

@@ -1,7 +1,7 @@
 # Round-1 evidence pass of the current kernels: GPU parity tests, smoke, bench line (+extras, +reference arm),
 # ncu launch list and one full-set capture of k_step (each ncu pass only after the same command exited 0 without ncu).
 set -x
-T=${TAG:-r1d}
+T=${TAG:-r1e}
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv
 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2

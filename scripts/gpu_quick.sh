@@ -1,3 +1,1 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-python scripts/kbench.py 2>&1 | tail -1
-CTR_NO_SORT=1 python scripts/kbench.py 2>&1 | tail -1
+for f in gym-ctr-reach_b200/variants/lib_*.so; do CTR_B200_LIB=$PWD/$f python scripts/kbench.py 2>&1 | tail -1; done
