@@ -739,7 +739,7 @@ __global__ void __launch_bounds__(256) k_fma_peak(T* out, int iters, T b, T c) {
     for (int k = 0; k < 8; ++k) a[k] = (T)(threadIdx.x + k) * (T)1e-3;
     for (int i = 0; i < iters; ++i) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) a[k] = a[k] * b + c;
+        for (int k = 0; k < 8; ++k) a[k] = fma_t(a[k], b, c);   // explicit: the library is built with -fmad=false
     }
     T s = 0;
 #pragma unroll
