@@ -34,6 +34,44 @@ F_RHS, F_STEP, F_SECTION, F_NONFK = 120.0, 1290.0, 200.0, 350.0
 BYTES_PER_STEP = 250.0          # joints/action/goal/t in, joints/achieved/obs/reward/error/flags/t out
 
 
+_JSON_OUT = None
+
+
+def claim_stdout():
+    """Keep stdout for the ONE JSON line: libraries write there too (under torchrun NCCL prints its version banner to fd 1
+    ahead of the result line), so fd 1 is pointed at stderr for the rest of the run and the line goes to the saved descriptor."""
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), 'w')
+        os.dup2(2, 1)
+        sys.stdout = sys.stderr
+
+
+def emit(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
+def bind_to_gpu_numa_node(index):
+    """Run this rank (and first-touch its pinned host buffers) on the CPUs NVML reports as local to GPU `index`: with 8 ranks
+    on one box the end-to-end path is bound by host memory / PCIe placement, not by the GPU.  Returns the cpu list or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (m >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return sorted(cpus)
+    except Exception:
+        pass
+    return None
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -134,7 +172,7 @@ def reference_arm(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -202,6 +240,7 @@ def gpu_arm(args):
             print("warning: WORLD_SIZE=%d but --gpus %d; using WORLD_SIZE" % (world, args.gpus), file=sys.stderr)
     dev = torch.device('cuda', local_rank)
     torch.cuda.set_device(dev)
+    numa_cpus = bind_to_gpu_numa_node(local_rank) if world > 1 else None
     N = args.envs_per_gpu
     total = N * world
     env = cdist.make_sharded_vec_env(total, rank=rank, world_size=world, device=local_rank, integrator=args.integrator,
@@ -318,6 +357,7 @@ def gpu_arm(args):
                        "l2": "flushed between timed steps (256 MiB memset outside the event pairs)",
                        "timing": "one CUDA event pair per step on the launch stream, summed; max over ranks"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
+                    "host_cpus_rank0": (("%d cpus local to the GPU (NVML affinity)" % len(numa_cpus)) if numa_cpus else "unbound"),
                     "api": "CtrReachVecEnv.step_host -> ctr_step_host (pinned host buffers, synchronous; chunks pipelined H2D / k_step / D2H, replayed as a CUDA graph)", "checksum": checksum},
             "gpu_launches": int(launches),
             "clocks": clocks,
@@ -349,7 +389,7 @@ def gpu_arm(args):
             line["extra"] = extras(args, dev, pool)
     env.close()
     if line is not None:
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -447,6 +487,7 @@ def main():
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--extras', action='store_true', help='also time the other BASELINE.json configs (1 GPU)')
     args = ap.parse_args()
+    claim_stdout()
     if args.impl == 'reference':
         return reference_arm(args)
     return gpu_arm(args)

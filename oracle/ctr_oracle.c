@@ -265,6 +265,34 @@ int ctr_oracle_fk(const double *tc, const double *q, double rtol, double atol, d
     return status;
 }
 
+/* per-section step attempts of one FK (analysis of the GPU kernel's lock-step cost, oracle/lockstep_sim.py):
+ * att[MAXSEC] = accepted + rejected steps of each kept section, returns the section count */
+int ctr_oracle_fk_attempts(const double *tc, const double *q, double rtol, double atol, int *att) {
+    double S[MAXSEC], EI[NT][MAXSEC], GJ[NT][MAXSEC], Ux[NT][MAXSEC], Uy[NT][MAXSEC];
+    int m = segment(tc, q, S, EI, GJ, Ux, Uy);
+    double y[NY];
+    memset(y, 0, sizeof y);
+    y[3] = q[3]; y[4] = q[4]; y[5] = q[5];
+    double ca = cos(q[3]), sa = sin(q[3]);
+    y[9] = ca; y[10] = -sa; y[12] = sa; y[13] = ca; y[17] = 1.0;
+    double prev = 0.0;
+    for (int k = 0; k < MAXSEC; ++k) att[k] = 0;
+    for (int k = 0; k < m; ++k) {
+        sec_t c;
+        cnt_t cnt = {0, 0, 0};
+        for (int i = 0; i < NT; ++i) { c.ei[i] = EI[i][k]; c.gj[i] = GJ[i][k]; c.ux0[i] = Ux[i][k]; c.uy0[i] = Uy[i][k]; }
+        double t0 = prev, tf = S[k] - 1e-6;
+        if (tf < t0) { double z = t0; t0 = tf; tf = z; }
+        dp45_section(&c, t0, tf, y, rtol, atol, &cnt);
+        att[k] = cnt.nacc + cnt.nrej;
+        prev = S[k];
+    }
+    return m;
+}
+typedef struct { const double *tc; const double *q; int32_t *att; } att_ctx;
+static void att_range(void *p, int64_t lo, int64_t hi, int *bad);
+int ctr_oracle_fk_attempts_batch(const double *tc, const double *q, int64_t n, int32_t *att, int nthreads);
+
 /* ---- minimal pthread parallel-for (libgomp is not in this image) ------------------------------- */
 typedef void (*range_fn)(void *ctx, int64_t lo, int64_t hi, int *bad);
 typedef struct { range_fn fn; void *ctx; int64_t lo, hi; int bad; } job_t;
@@ -303,6 +331,20 @@ int ctr_oracle_fk_batch(const double *tcs, const int32_t *system, const double *
                         double *state, int32_t *info, int nthreads) {
     fk_ctx c = {tcs, system, q, rtol, atol, state, info};
     return parallel_for(fk_range, &c, n, nthreads);
+}
+
+static void att_range(void *p, int64_t lo, int64_t hi, int *bad) {
+    att_ctx *c = (att_ctx *)p;
+    (void)bad;
+    for (int64_t i = lo; i < hi; ++i) {
+        int a[MAXSEC];
+        ctr_oracle_fk_attempts(c->tc, c->q + 6 * i, 1e-3, 1e-6, a);
+        for (int k = 0; k < MAXSEC; ++k) c->att[MAXSEC * i + k] = a[k];
+    }
+}
+int ctr_oracle_fk_attempts_batch(const double *tc, const double *q, int64_t n, int32_t *att, int nthreads) {
+    att_ctx c = {tc, q, att};
+    return parallel_for(att_range, &c, n, nthreads);
 }
 
 /* ---- obs.py:166-183 x n_substeps (ctr_reach_env.py:134-135), float32 arithmetic ------------------
