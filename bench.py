@@ -469,6 +469,45 @@ def extras(args, dev, pool):
     res["cfg4_her_relabel_2^20"] = {"us_per_call": us, "GB/s": 80.0 * m / (us * 1e-6) / 1e9, "bytes_per_transition": 80,
                                     "note": "back-to-back, 84 MB working set is L2 resident"}
     e.close()
+    # hindsight replay on the device -- store one step of 131072 envs, sample 2^20 'future'-relabelled
+    # transitions (n_sampled_goal 4).  HBM-bound byte movers; bytes counted from the rows each thread reads and writes.
+    from ctr_reach_envs.her import HerReplay
+    e = CtrReachVecEnv(ENVS_PER_GPU, device=dev.index, **k)
+    e.goal_tolerance.current_tol = args.tol
+    e.reset()
+    D, cap = e.obs_dim, 32
+    rep = HerReplay(e, cap, n_sampled_goal=4, seed=1)
+    rep.begin()
+    acts = pool[:4]
+    for i in range(cap + 4):                       # fill the ring (episodes end and restart on the way)
+        e.step(acts[i % 4])
+        rep.store(acts[i % 4])
+    torch.cuda.synchronize(dev)
+    s, t = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for i in range(20):
+        rep.store(acts[i % 4])
+    t.record()
+    torch.cuda.synchronize(dev)
+    us = s.elapsed_time(t) / 20 * 1e3
+    store_bytes = (5 * D * 8 + 8 * 24 + 2 * 24 + 2 * 8 + 2 + 4 * 4)   # obs/cur/terminal in, obs/next/cur out; goals; action; reward; flags; counters
+    res["her_store_131072_envs"] = {"us_per_call": us, "GB/s": store_bytes * ENVS_PER_GPU / (us * 1e-6) / 1e9,
+                                    "bytes_per_transition": store_bytes, "bound": "hbm (coalesced)"}
+    batch = rep.alloc_batch(m)
+    for c in range(3):
+        rep.sample(m, out=batch, call=c)
+    s.record()
+    for c in range(20):
+        rep.sample(m, out=batch, call=c)
+    t.record()
+    torch.cuda.synchronize(dev)
+    us = s.elapsed_time(t) / 20 * 1e3
+    sample_bytes = 2 * (2 * D * 8 + 3 * 24 + 24 + 8 + 1) + 24 + 8 + 16        # gather in + batch out + donor goal + ring counters + src
+    res["her_sample_2^20_future_k4"] = {"us_per_call": us, "transitions/s": m / (us * 1e-6), "GB/s": sample_bytes * m / (us * 1e-6) / 1e9,
+                                        "bytes_per_transition": sample_bytes,
+                                        "bound": "hbm (gather: one 32-byte sector per 8-byte row element read)",
+                                        "ring_MB": cap * ENVS_PER_GPU * (2 * D * 8 + 3 * 24 + 24 + 8 + 1 + 8) / 1e6}
+    e.close()
     return res
 
 

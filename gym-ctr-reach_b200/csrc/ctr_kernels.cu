@@ -19,6 +19,7 @@
 
 #include "../../include/ctr_b200.h"
 #include "ctr_device.cuh"
+#include "ctr_her.cuh"
 
 using namespace ctr;
 
@@ -796,7 +797,6 @@ struct ctr_handle {
     int sm_count;
     // lazily allocated staging for host calls
     float* stage_action;
-    double* stage_fk_in;
     int64_t stage_fk_cap;
     void* stage_fk_dev;
 };
@@ -959,7 +959,6 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     h->use_params = 0;
     h->launches = 0;
     h->stage_action = nullptr;
-    h->stage_fk_in = nullptr;
     h->stage_fk_cap = 0;
     h->stage_fk_dev = nullptr;
     cudaDeviceProp prop;
@@ -1074,8 +1073,7 @@ int ctr_destroy(ctr_handle* h) {
     cudaSetDevice(h->device);
     cudaDeviceSynchronize();
     for (void* ptr : h->allocs) cudaFree(ptr);
-    if (h->stage_action) cudaFreeHost(h->stage_action);
-    if (h->stage_fk_in) cudaFreeHost(h->stage_fk_in);
+    if (h->stage_action) cudaFree(h->stage_action);      // device staging of ctr_step_host (cudaMalloc, step_host_impl)
     if (h->stage_fk_dev) cudaFree(h->stage_fk_dev);
     if (h->stream) cudaStreamDestroy(h->stream);
     for (int k = 1; k <= N_COMPUTE_STREAMS; ++k) {
@@ -1089,7 +1087,12 @@ int ctr_destroy(ctr_handle* h) {
         cudaGraphDestroy(g.graph);
     }
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    const cudaError_t pending = cudaGetLastError();      // never hand a stale error to the next handle's first launch check
     delete h;
+    if (pending != cudaSuccess) {
+        g_err = std::string("ctr_destroy: ") + cudaGetErrorString(pending);
+        return 2;
+    }
     return 0;
 }
 
@@ -1534,6 +1537,76 @@ int ctr_stats_reset(ctr_handle* h, void* stream) {
     if (!h) CTR_FAIL("null handle");
     CTR_CUDA(cudaSetDevice(h->device));
     CTR_CUDA(cudaMemsetAsync(h->p.stats, 0, sizeof(double) * N_STATS, (cudaStream_t)stream));
+    return 0;
+}
+
+// ---- hindsight replay (kernels in ctr_her.cuh) ------------------------------------------------
+static int her_check(const ctr_handle* h, const ctr_her_ring* r) {
+    if (!h || !r) CTR_FAIL("null argument");
+    if (r->n_envs != h->n) CTR_FAIL("ring.n_envs differs from the handle's environment count");
+    if (r->capacity < 1) CTR_FAIL("ring.capacity must be >= 1");
+    if (r->obs_dim != h->obs_dim) CTR_FAIL("ring.obs_dim differs from ctr_obs_dim()");
+    if (!r->obs || !r->next_obs || !r->achieved || !r->next_achieved || !r->desired || !r->action || !r->reward ||
+        !r->done || !r->t_in_ep || !r->ep_len || !r->cur_obs || !r->cur_achieved || !r->cur_desired || !r->cur_t)
+        CTR_FAIL("ring has a null buffer");
+    return 0;
+}
+static HerSrc her_src(const ctr_handle* h) {
+    HerSrc s;
+    s.obs = h->p.obs;
+    s.achieved = h->p.achieved;
+    s.desired = h->p.desired_goal;
+    s.terminal_obs = h->p.terminal_obs;
+    s.terminal_achieved = h->p.terminal_achieved;
+    s.reward = h->p.reward;
+    s.done = h->p.done;
+    s.auto_reset = h->cfg.auto_reset;
+    return s;
+}
+
+int ctr_her_begin(ctr_handle* h, const ctr_her_ring* ring, void* stream) {
+    int rc = her_check(h, ring);
+    if (rc) return rc;
+    CTR_CUDA(cudaSetDevice(h->device));
+    k_her_begin<<<(int)((h->n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(*ring, her_src(h));
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int ctr_her_store(ctr_handle* h, const ctr_her_ring* ring, const float* action_dev, int64_t stride_field,
+                  int64_t stride_env, int64_t slot, void* stream) {
+    int rc = her_check(h, ring);
+    if (rc) return rc;
+    if (!action_dev) CTR_FAIL("null action");
+    if (slot < 0 || slot >= ring->capacity) CTR_FAIL("slot out of range");
+    CTR_CUDA(cudaSetDevice(h->device));
+    k_her_store<<<(int)((h->n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(*ring, her_src(h), action_dev, stride_field,
+                                                                            stride_env, slot);
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int ctr_her_sample(ctr_handle* h, const ctr_her_ring* ring, int64_t n_stored, int64_t newest_slot, int32_t n_sampled_goal,
+                   int32_t rewrite_error, double tol, uint64_t seed, uint64_t call, const ctr_her_batch* b, void* stream) {
+    int rc = her_check(h, ring);
+    if (rc) return rc;
+    if (!b) CTR_FAIL("null batch");
+    if (b->m <= 0) return 0;
+    if (n_stored < 1 || n_stored > ring->capacity) CTR_FAIL("n_stored must be in [1, capacity]");
+    if (newest_slot < 0 || newest_slot >= ring->capacity) CTR_FAIL("newest_slot out of range");
+    if (n_sampled_goal < 0) CTR_FAIL("n_sampled_goal must be >= 0");
+    if (!b->obs || !b->next_obs || !b->achieved || !b->next_achieved || !b->desired || !b->action || !b->reward ||
+        !b->done || !b->src || !b->goal_src)
+        CTR_FAIL("batch has a null buffer");
+    CTR_CUDA(cudaSetDevice(h->device));
+    if (tol < 0) tol = h->tol;
+    k_her_sample<<<(int)((b->m + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        *ring, *b, n_stored, newest_slot, n_sampled_goal, rewrite_error, tol, h->cfg.reward_mode,
+        make_uint2((unsigned)seed, (unsigned)(seed >> 32)), make_uint2((unsigned)call, (unsigned)(call >> 32)));
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
     return 0;
 }
 

@@ -25,7 +25,8 @@ EXPORTS = ['ctr_last_error', 'ctr_abi_version', 'ctr_create', 'ctr_destroy', 'ct
            'ctr_system_constants', 'ctr_set_tolerance', 'ctr_get_tolerance', 'ctr_seed', 'ctr_set_tube_params', 'ctr_fk',
            'ctr_fk_host', 'ctr_set_action', 'ctr_set_state_host', 'ctr_reset', 'ctr_step', 'ctr_step_strided',
            'ctr_step_host', 'ctr_step_host_packed', 'ctr_reset_host', 'ctr_compute_reward', 'ctr_relabel', 'ctr_stats', 'ctr_stats_reset',
-           'ctr_launch_count', 'ctr_work_counters', 'ctr_measure_fma_peak']
+           'ctr_launch_count', 'ctr_work_counters', 'ctr_measure_fma_peak', 'ctr_her_begin', 'ctr_her_store',
+           'ctr_her_sample']
 
 
 class CtrConfig(ctypes.Structure):
@@ -52,6 +53,20 @@ class CtrConfig(ctypes.Structure):
         ('seed', ctypes.c_uint64),
         ('env_offset', ctypes.c_int64),
     ]
+
+
+class CtrHerRing(ctypes.Structure):
+    """ctr_her_ring (include/ctr_b200.h): caller-owned, time-major replay ring."""
+    _fields_ = [('n_envs', ctypes.c_int64), ('capacity', ctypes.c_int64), ('obs_dim', ctypes.c_int32), ('pad_', ctypes.c_int32)] + [
+        (k, ctypes.c_void_p) for k in ('obs', 'next_obs', 'achieved', 'next_achieved', 'desired', 'action', 'reward', 'done',
+                                       't_in_ep', 'ep_len', 'cur_obs', 'cur_achieved', 'cur_desired', 'cur_t')]
+
+
+class CtrHerBatch(ctypes.Structure):
+    """ctr_her_batch (include/ctr_b200.h): one sampled batch, SoA [rows][m]."""
+    _fields_ = [('m', ctypes.c_int64)] + [
+        (k, ctypes.c_void_p) for k in ('obs', 'next_obs', 'achieved', 'next_achieved', 'desired', 'action', 'reward', 'done',
+                                       'src', 'goal_src')]
 
 
 _lib = None
@@ -101,6 +116,10 @@ def load():
     lib.ctr_measure_fma_peak.argtypes = [i32, i32, ctypes.POINTER(f64)]
     lib.ctr_launch_count.restype = i64
     lib.ctr_launch_count.argtypes = [vp]
+    lib.ctr_her_begin.argtypes = [vp, ctypes.POINTER(CtrHerRing), vp]
+    lib.ctr_her_store.argtypes = [vp, ctypes.POINTER(CtrHerRing), vp, i64, i64, i64, vp]
+    lib.ctr_her_sample.argtypes = [vp, ctypes.POINTER(CtrHerRing), i64, i64, i32, i32, f64, ctypes.c_uint64, ctypes.c_uint64,
+                                   ctypes.POINTER(CtrHerBatch), vp]
     for name in EXPORTS:
         if name not in ('ctr_last_error', 'ctr_num_envs', 'ctr_obs_dim', 'ctr_get_tolerance', 'ctr_launch_count'):
             getattr(lib, name).restype = ctypes.c_int

@@ -181,6 +181,55 @@ int ctr_measure_fma_peak(int32_t device, int32_t precision, double *tflops_out);
 /* Number of kernels launched by this handle so far (bench.py's gpu_launches claim). */
 int64_t ctr_launch_count(const ctr_handle *h);
 
+/* ---- hindsight replay on the device --------------------------------------------------------
+ * Replaces what the reference delegates to stable_baselines' HER wrapper (third party, not vendored, version not
+ * pinned: setup.py:5; call sites src/utils.py:5-7,27-28; settings saved_policies/.../config.yml: goal_selection_strategy
+ * future, n_sampled_goal 4, buffer_size 500000, batch_size 256).  The relabelled reward is the reference's own
+ * compute_reward (ctr_reach_env.py:160-170).  The ring is CALLER-OWNED device memory, time major: transition
+ * (slot, env) lives at column slot * n_envs + env of every SoA row, rows are capacity * n_envs apart. */
+typedef struct {
+    int64_t n_envs, capacity;      /* capacity = number of step slots                                            */
+    int32_t obs_dim;               /* D = ctr_obs_dim()                                                          */
+    int32_t pad_;
+    double *obs, *next_obs;        /* f64 [D][capacity*n]  'observation' before / after the step                 */
+    double *achieved, *next_achieved, *desired;   /* f64 [3][capacity*n]                                         */
+    float *action;                 /* f32 [6][capacity*n]                                                        */
+    double *reward;                /* f64 [capacity*n]                                                           */
+    uint8_t *done;                 /* u8  [capacity*n]                                                           */
+    int32_t *t_in_ep;              /* i32 [capacity*n]  1-based index of the transition inside its episode        */
+    int32_t *ep_len;               /* i32 [capacity*n]  length of its episode; 0 while the episode is still open  */
+    double *cur_obs;               /* f64 [D][n]  observation the NEXT stored transition starts from              */
+    double *cur_achieved, *cur_desired;           /* f64 [3][n]                                                  */
+    int32_t *cur_t;                /* i32 [n]     transitions stored so far for the open episode of each env     */
+} ctr_her_ring;
+
+typedef struct {                   /* one sampled batch, caller-owned device memory, SoA [rows][m]                */
+    int64_t m;
+    double *obs, *next_obs;        /* f64 [D][m]                                                                 */
+    double *achieved, *next_achieved, *desired;   /* f64 [3][m]; desired is the (possibly relabelled) goal        */
+    float *action;                 /* f32 [6][m]                                                                 */
+    double *reward;                /* f64 [m]                                                                    */
+    uint8_t *done;                 /* u8  [m]   0 for relabelled transitions                                     */
+    int64_t *src, *goal_src;       /* i64 [m]   ring column of the transition / of the goal's donor (-1: original) */
+} ctr_her_batch;
+
+/* Start recording: cur_* <- the handle's current obs / achieved / desired, cur_t <- 0 (call after ctr_reset). */
+int ctr_her_begin(ctr_handle *h, const ctr_her_ring *ring, void *stream);
+/* Store the transition of the ctr_step that was just enqueued on `stream` into ring slot `slot`; action as for
+ * ctr_step_strided.  Finished episodes (done) take next_obs / next_achieved from the terminal buffers, get their
+ * ep_len back-filled, and the env's cur_* continue from the auto-reset state. */
+int ctr_her_store(ctr_handle *h, const ctr_her_ring *ring, const float *action_dev, int64_t stride_field,
+                  int64_t stride_env, int64_t slot, void *stream);
+/* Sample batch->m transitions uniformly from the `n_stored` newest slots (newest = `newest_slot`) with the 'future'
+ * strategy: with probability k / (k + 1), k = n_sampled_goal, the desired goal is replaced by the achieved goal the
+ * same episode reaches after a uniformly drawn later-or-equal transition (never for the last transition of an episode),
+ * reward = compute_reward(next_achieved, goal) with tolerance `tol` (< 0: the handle's), done = 0.  rewrite_error != 0
+ * also sets obs[9:12] / next_obs[9:12] = goal - achieved / next_achieved (extension; the reference's wrapper swaps only
+ * the desired_goal entry).  Draws are Philox4x32-10 keyed by (seed; sample index, call): reproducible on the host. */
+int ctr_her_sample(ctr_handle *h, const ctr_her_ring *ring, int64_t n_stored, int64_t newest_slot,
+                   int32_t n_sampled_goal, int32_t rewrite_error, double tol, uint64_t seed, uint64_t call,
+                   const ctr_her_batch *batch, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

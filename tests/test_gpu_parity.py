@@ -610,6 +610,28 @@ def test_host_step_entry_point_matches_device_path(vec_factory):
         assert torch.equal(envs[0].buffer(k), envs[1].buffer(k)), k
 
 
+def test_destroy_after_host_step_is_clean():
+    """Regression: ctr_destroy freed the device staging buffer of ctr_step_host with cudaFreeHost; the 'invalid argument' stayed
+    pending and failed the NEXT handle's first launch check (and leaked 24 B/env of device memory per handle)."""
+    from ctr_reach_envs import _lib
+    from conftest import make_vec
+    env = make_vec(1280)
+    env.reset()
+    out = env.alloc_host_outputs()
+    act = np.zeros((6, 1280), dtype=np.float32)
+    env.step_host(act, out)
+    free0 = torch.cuda.mem_get_info()[0]
+    torch.cuda.synchronize()
+    env._closed = True
+    env._buf.clear()
+    assert env.lib.ctr_destroy(env.handle) == 0, _lib.load().ctr_last_error()
+    nxt = make_vec(1280)
+    nxt.reset()                                   # the call that used to raise 'launch_reset: ... invalid argument'
+    torch.cuda.synchronize()
+    nxt.close()
+    assert torch.cuda.mem_get_info()[0] >= free0  # nothing of the destroyed handle is still allocated
+
+
 def test_error_paths(vec_factory):
     from ctr_reach_envs import _lib
     lib = _lib.load()
