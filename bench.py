@@ -469,6 +469,27 @@ def extras(args, dev, pool):
     res["cfg4_her_relabel_2^20"] = {"us_per_call": us, "GB/s": 80.0 * m / (us * 1e-6) / 1e9, "bytes_per_transition": 80,
                                     "note": "back-to-back, 84 MB working set is L2 resident"}
     e.close()
+    # backbone shape (Model.r / tip_pos) of 131072 configurations, next to the plain FK of the same joints
+    e = CtrReachVecEnv(ENVS_PER_GPU, device=dev.index, **k)
+    e.reset()
+    qj = e.buffer('joints').t().to(torch.float64).contiguous()
+    for fn, name in ((lambda: e.forward_kinematics(qj), "fk_only_131072"), (lambda: e.backbone_shape(qj), "fk_shape_131072")):
+        for _ in range(3):
+            out_ = fn()
+        torch.cuda.synchronize(dev)
+        s, t = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(10):
+            out_ = fn()
+        t.record()
+        torch.cuda.synchronize(dev)
+        us = s.elapsed_time(t) / 10 * 1e3
+        res[name] = {"us_per_call": us, "configs/s": ENVS_PER_GPU / (us * 1e-6),
+                     "note": "includes the torch-side transposes / output allocation of the python front-end"}
+        if name.startswith("fk_shape"):
+            pts = float(out_[1].double().mean())
+            res[name].update({"mean_samples": pts, "GB/s_written": 24.0 * pts * ENVS_PER_GPU / (us * 1e-6) / 1e9})
+    e.close()
     # hindsight replay on the device -- store one step of 131072 envs, sample 2^20 'future'-relabelled
     # transitions (n_sampled_goal 4).  HBM-bound byte movers; bytes counted from the rows each thread reads and writes.
     from ctr_reach_envs.her import HerReplay

@@ -210,6 +210,28 @@ __constant__ float c_dp32[DP_NCOEF] = {
     (float)(35.0 / 384), (float)(500.0 / 1113), (float)(125.0 / 192), (float)(-2187.0 / 6784), (float)(11.0 / 84),
     (float)(-71.0 / 57600), (float)(71.0 / 16695), (float)(-71.0 / 1920), (float)(17253.0 / 339200), (float)(-22.0 / 525),
     (float)(1.0 / 40)};
+// Dense-output matrix of RK45 (rk.py: RK45.P, 7 stages x 4 powers; row 1 is zero), used only by the backbone-shape variant.
+__constant__ double c_dpP[28] = {
+    1, -8048581381.0 / 2820520608.0, 8663915743.0 / 2820520608.0, -12715105075.0 / 11282082432.0,
+    0, 0, 0, 0,
+    0, 131558114200.0 / 32700410799.0, -68118460800.0 / 10900136933.0, 87487479700.0 / 32700410799.0,
+    0, -1754552775.0 / 470086768.0, 14199869525.0 / 1410260304.0, -10690763975.0 / 1880347072.0,
+    0, 127303824393.0 / 49829197408.0, -318862633887.0 / 49829197408.0, 701980252875.0 / 199316789632.0,
+    0, -282668133.0 / 205662961.0, 2019193451.0 / 616988883.0, -1453857185.0 / 822651844.0,
+    0, 40617522.0 / 29380423.0, -110615467.0 / 29380423.0, 69997945.0 / 29380423.0};
+constexpr int SHAPE_SAMPLES = 30;      // model.py:143: np.linspace(span[k], span[k+1] - 1e-6, num=30)
+
+// Where the backbone samples of this lane's position component go: sample p of the env at base[p * stride], p < max_pts.
+struct ShapeOut {
+    double* base;
+    int64_t stride;
+    int max_pts;
+};
+// abscissa i of np.linspace(a, b, 30): i * step + a (two roundings), the last one is b itself
+__device__ __forceinline__ double shape_abscissa(int i, double a, double step, double b) {
+    return (i == SHAPE_SAMPLES - 1) ? b : __dadd_rn(__dmul_rn((double)i, step), a);
+}
+
 template <typename T> __device__ __forceinline__ T dpc(int i);
 template <> __device__ __forceinline__ double dpc<double>(int i) { return c_dp64[i]; }
 template <> __device__ __forceinline__ float dpc<float>(int i) { return c_dp32[i]; }
@@ -377,6 +399,7 @@ __device__ __forceinline__ double min_step_of(double t) {
 
 struct FkInfo {
     int nfev, nacc, nrej, nsec, failed;
+    int shape_secs;   // sections whose 30 backbone samples were written (SHAPE variant only)
 };
 
 // ---- forward kinematics (model.py:30-70, 119-174) for the lane group ----------------------------------------
@@ -428,9 +451,13 @@ __device__ __forceinline__ bool advance_section(const GroupScratch& gs, const do
 
 // INTEG 0: scipy RK45 restated (rk.py rk_step/_step_impl, common.py select_initial_step), per-env adaptive.
 // On return lane j holds y = {uz_j, alpha_j, r_j, R_j0..2} at the tip.
-template <typename T, bool SLOW, bool UY0>
+// SHAPE: additionally sample r_j at the 30 abscissae of every section through scipy's dense output (rk.py RkDenseOutput:
+// y_old + h * Q . [x, x^2, x^3, x^4], Q = K^T P, x = (s - t_old) / h), as solve_ivp(t_eval=...) does for Model.r
+// (model.py:143-158, ivp.py t_eval handling: the samples in (t_old, t_new] after every accepted step).
+template <typename T, bool SLOW, bool UY0, bool SHAPE = false>
 __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const GroupScratch& gs, const double* der,
-                                        const double* alpha, double rtol_d, double atol_d, T (&y)[6], FkInfo& info) {
+                                        const double* alpha, double rtol_d, double atol_d, T (&y)[6], FkInfo& info,
+                                        const ShapeOut shape = ShapeOut{nullptr, 0, 0}) {
     const int j = id.j;
     const int mn = (j == 2) ? 0 : j + 1, mp = (j == 0) ? 2 : j - 1;
     initial_state<T>(j, alpha, y);
@@ -451,6 +478,9 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
     double t = 0.0, tf = 0.0, h_abs = 0.0;
     bool done = !valid, need_sec = true, rejected = false;
     bool first = true;   // warp-uniform: no RHS has been evaluated yet, so slot 0 needs the trigonometry
+    int sh_i = SHAPE_SAMPLES, sh_sec = -1;          // SHAPE: next abscissa of the current section, sections started
+    double sh_a = 0.0, sh_step = 0.0;
+    info.shape_secs = 0;
 
     for (;;) {
         bool init = false;
@@ -461,6 +491,12 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
                     need_sec = false;
                     rejected = false;
                     info.nsec += 1;
+                    if (SHAPE) {
+                        sh_a = t;
+                        sh_step = __ddiv_rn(__dsub_rn(tf, t), (double)(SHAPE_SAMPLES - 1));
+                        sh_i = 0;
+                        sh_sec += 1;
+                    }
                 }
             }
         }
@@ -585,6 +621,34 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
             info.nfev += 6;
             h_abs *= factor;
             if (accept) {
+                if (SHAPE) {
+                    // Q for the lane's position component r_j (index 2): Q[p] = sum_s K_s[2] P[s][p]
+                    double Q[4];
+#pragma unroll
+                    for (int pw = 0; pw < 4; ++pw) {
+                        double q = __dmul_rn((double)f[2], c_dpP[pw]);
+                        q = __dadd_rn(q, __dmul_rn((double)k2[2], c_dpP[4 + pw]));
+                        q = __dadd_rn(q, __dmul_rn((double)k3[2], c_dpP[8 + pw]));
+                        q = __dadd_rn(q, __dmul_rn((double)k4[2], c_dpP[12 + pw]));
+                        q = __dadd_rn(q, __dmul_rn((double)k5[2], c_dpP[16 + pw]));
+                        q = __dadd_rn(q, __dmul_rn((double)k6[2], c_dpP[20 + pw]));
+                        Q[pw] = __dadd_rn(q, __dmul_rn((double)k7[2], c_dpP[24 + pw]));
+                    }
+                    while (sh_i < SHAPE_SAMPLES) {
+                        const double te = shape_abscissa(sh_i, sh_a, sh_step, tf);
+                        if (!(te <= t_new)) break;                                  // ivp.py: searchsorted(t_eval, t, 'right')
+                        const double x = __ddiv_rn(__dsub_rn(te, t), h_d);
+                        const double x2 = __dmul_rn(x, x), x3 = __dmul_rn(x2, x), x4 = __dmul_rn(x3, x);   // np.cumprod
+                        double acc = __dmul_rn(Q[0], x);
+                        acc = __dadd_rn(acc, __dmul_rn(Q[1], x2));
+                        acc = __dadd_rn(acc, __dmul_rn(Q[2], x3));
+                        acc = __dadd_rn(acc, __dmul_rn(Q[3], x4));
+                        const int pt = sh_sec * SHAPE_SAMPLES + sh_i;
+                        if (pt < shape.max_pts) shape.base[(int64_t)pt * shape.stride] = __dadd_rn(__dmul_rn(h_d, acc), (double)y[2]);
+                        sh_i += 1;
+                    }
+                    info.shape_secs = sh_sec + 1;
+                }
 #pragma unroll
                 for (int i = 0; i < 6; ++i) {
                     y[i] = Y[i];
@@ -702,6 +766,17 @@ __device__ __forceinline__ void fk_group(const LaneId& id, bool valid, GroupScra
         else fk_rk4<T, false, UY0>(id, valid, gs, der, alpha, rk4_steps, y, info);
     }
     __syncwarp();   // the scratch slot may be rebuilt by the caller's next FK
+}
+
+// FK with backbone samples (float64 parity integrator only): same section table and integrator as fk_group.
+__device__ __forceinline__ void fk_group_shape(const LaneId& id, bool valid, GroupScratch& gs, const double* L,
+                                               const double* Lc, const double* der, const double* beta, const double* alpha,
+                                               double rtol_d, double atol_d, double (&y)[6], FkInfo& info,
+                                               const ShapeOut shape) {
+    build_sections(L, Lc, beta, gs, id.j == 0);
+    if (needs_slow_trig(id.j, alpha)) fk_dp45<double, true, false, true>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info, shape);
+    else fk_dp45<double, false, false, true>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info, shape);
+    __syncwarp();
 }
 
 // ---- Obs.set_action x n_substeps (obs.py:166-183, ctr_reach_env.py:134-135), float32 arithmetic -------------

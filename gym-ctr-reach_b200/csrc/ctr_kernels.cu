@@ -235,6 +235,67 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk(const SysConst* __rest
     }
 }
 
+// Backbone shape: Model.r and tip_pos of the reference (model.py:66-68,137-172) -- 30 samples per
+// section from the integrator's dense output, and for every tube the first sample index whose abscissa reaches
+// L_k + beta_k - 1e-3 (the split points of r1 / r2 / r3).  shape f64 [3][max_pts][n], npts i32 [n], tip_idx i32 [3][n].
+__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk_shape(const SysConst* __restrict__ sys, int n_systems,
+                                                    const double* __restrict__ joints, const int32_t* __restrict__ system,
+                                                    const double* __restrict__ params, int64_t n, double rtol, double atol,
+                                                    int max_pts, double* __restrict__ shape, int32_t* __restrict__ npts,
+                                                    int32_t* __restrict__ tip_idx, double* __restrict__ tip,
+                                                    double* __restrict__ stats) {
+    __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
+    __shared__ GroupScratch s_gs[(BLOCK / 32) * SLOTS_PER_WARP];
+    stage_sys(s_sys, sys, n_systems);
+    const LaneId id = lane_id();
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t env = warp * ENVS_PER_WARP + id.g;
+    const bool valid = (id.g < ENVS_PER_WARP) && (env < n);
+    const int64_t e = valid ? env : 0;
+    int sysid = system ? system[e] : 0;
+    sysid = min(max(sysid, 0), n_systems - 1);
+    GroupScratch& gs = group_slot(s_gs, id);
+    double LL[6];
+    const double* der = env_consts(s_sys[sysid], params, n, e, params != nullptr, id.j == 0, gs, LL);
+    double beta[3], alpha[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        beta[i] = joints[(int64_t)i * n + e];
+        alpha[i] = joints[(int64_t)(3 + i) * n + e];
+    }
+    double y[6];
+    FkInfo info;
+    ShapeOut so;
+    so.base = shape + ((int64_t)id.j * max_pts) * n + e;
+    so.stride = n;
+    so.max_pts = valid ? max_pts : 0;
+    fk_group_shape(id, valid, gs, LL, LL + 3, der, beta, alpha, rtol, atol, y, info, so);
+    if (valid) {
+        // tip_pos[j] = np.argmax(Length >= d_tip[j] - 1e-3) over the concatenated abscissae (0 when none qualifies)
+        const double thr = __dsub_rn(__dadd_rn(pick3(id.j, LL[0], LL[1], LL[2]), pick3(id.j, beta[0], beta[1], beta[2])), 1e-3);
+        const int nsec = gs.nsec & 0xff;
+        int found = 0;
+        bool hit = false;
+        for (int k = 0; k < nsec && !hit; ++k) {
+            const double a = gs.t0[k], b = gs.tf[k];
+            const double step = __ddiv_rn(__dsub_rn(b, a), (double)(SHAPE_SAMPLES - 1));
+            for (int i = 0; i < SHAPE_SAMPLES; ++i) {
+                if (shape_abscissa(i, a, step, b) >= thr) {
+                    found = k * SHAPE_SAMPLES + i;
+                    hit = true;
+                    break;
+                }
+            }
+        }
+        tip_idx[(int64_t)id.j * n + env] = found;
+        if (tip) tip[(int64_t)id.j * n + env] = y[2];
+        if (id.j == 0) {
+            npts[env] = info.shape_secs * SHAPE_SAMPLES;
+            if (info.failed && stats) atomicAdd(stats + ST_FK_FAILED, 1.0);
+        }
+    }
+}
+
 template <typename T, int INTEG>
 __device__ __forceinline__ void reset_envs(const KArgs& a, const LaneId& id, const SysConst* s_sys, GroupScratch* s_gs,
                                            int64_t env, bool valid, const double* __restrict__ goal,
@@ -1605,6 +1666,21 @@ int ctr_her_sample(ctr_handle* h, const ctr_her_ring* ring, int64_t n_stored, in
     k_her_sample<<<(int)((b->m + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
         *ring, *b, n_stored, newest_slot, n_sampled_goal, rewrite_error, tol, h->cfg.reward_mode,
         make_uint2((unsigned)seed, (unsigned)(seed >> 32)), make_uint2((unsigned)call, (unsigned)(call >> 32)));
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---- backbone shape ---------------------------------------------------------------------------
+int ctr_fk_shape(ctr_handle* h, const double* joints_dev, const int32_t* system_dev, const double* params_dev, int64_t n,
+                 int32_t max_pts, double* shape_dev, int32_t* npts_dev, int32_t* tip_idx_dev, double* tip_dev, void* stream) {
+    if (!h || !joints_dev || !shape_dev || !npts_dev || !tip_idx_dev) CTR_FAIL("null argument");
+    if (max_pts < 1) CTR_FAIL("max_pts must be >= 1");
+    if (n <= 0) return 0;
+    CTR_CUDA(cudaSetDevice(h->device));
+    k_fk_shape<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(h->sys_dev, h->cfg.n_systems, joints_dev, system_dev, params_dev,
+                                                               n, h->cfg.rtol, h->cfg.atol, max_pts, shape_dev, npts_dev,
+                                                               tip_idx_dev, tip_dev, h->p.stats);
     h->launches += 1;
     CTR_CUDA(cudaGetLastError());
     return 0;

@@ -240,6 +240,27 @@ class CtrReachVecEnv(object):
                                    _lib.ptr(tip), _lib.ptr(R), _lib.ptr(info), self._stream()))
         return (tip.t(), R.t(), info.t()) if return_info else tip.t()
 
+    def backbone_shape(self, joints, system=None, max_pts=270):
+        """Batched Model.r / tip_pos (model.py:66-68,137-172): joints (n, 6) -> r (n, max_pts, 3) float64 (30 samples per
+        section, rows past npts[i] are unspecified), npts (n,), tip_idx (n, 3), tip (n, 3).  split_backbone() gives r1, r2, r3."""
+        q = torch.as_tensor(joints, dtype=torch.float64, device=self.device).reshape(-1, 6).t().contiguous()
+        n = q.shape[1]
+        s = None if system is None else torch.as_tensor(system, dtype=torch.int32, device=self.device).expand(n).contiguous()
+        shape = torch.zeros((3, max_pts, n), dtype=torch.float64, device=self.device)
+        npts = torch.empty(n, dtype=torch.int32, device=self.device)
+        tip_idx = torch.empty((3, n), dtype=torch.int32, device=self.device)
+        tip = torch.empty((3, n), dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.ctr_fk_shape(self.handle, _lib.ptr(q), _lib.ptr(s), None, n, int(max_pts), _lib.ptr(shape),
+                                         _lib.ptr(npts), _lib.ptr(tip_idx), _lib.ptr(tip), self._stream()))
+        return shape.permute(2, 1, 0), npts, tip_idx.t(), tip.t()
+
+    @staticmethod
+    def split_backbone(r, npts, tip_idx):
+        """One configuration's (r [max_pts][3], npts, tip_idx [3]) -> r1, r2, r3 exactly as model.py:66-68 slices them."""
+        r = r[:int(npts)]
+        t0, t1, t2 = (int(v) for v in tip_idx)
+        return r[t1:t0 + 1], r[t2:t1 + 1], r[:t2 + 1]
+
     def set_tube_params(self, params):
         """Per-env derived constants (N, 18) = L, Lc, EI, GJ, Ux, Uy (x3 each) or None (model.py:20-28)."""
         if params is None:

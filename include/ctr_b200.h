@@ -181,6 +181,17 @@ int ctr_measure_fma_peak(int32_t device, int32_t precision, double *tflops_out);
 /* Number of kernels launched by this handle so far (bench.py's gpu_launches claim). */
 int64_t ctr_launch_count(const ctr_handle *h);
 
+/* ---- backbone shape --------------------------------------------------------------------------
+ * Model.r and tip_pos (ctr_reach_envs/envs/model.py:66-68,137-172): 30 samples per section of the backbone position
+ * (solve_ivp's t_eval = np.linspace(span[k], span[k+1] - 1e-6, 30), scipy RK45 dense output) and, per tube, the index of
+ * the first sample at or beyond L_k + beta_k - 1e-3, which splits r into r1 = r[tip1 : tip0 + 1], r2 = r[tip2 : tip1 + 1],
+ * r3 = r[: tip2 + 1].  Replaces the data the matplotlib renderer (envs/ctr_3d_graph.py) and src/utils.py:52-54 consume.
+ * joints f64 [6][n] -> shape f64 [3][max_pts][n] (samples past npts are left untouched), npts i32 [n] (30 x sections),
+ * tip_idx i32 [3][n], tip f64 [3][n] or NULL.  Always the float64 scipy-RK45 parity integrator.  A section table can hold
+ * 9 sections: max_pts = 270 never truncates. */
+int ctr_fk_shape(ctr_handle *h, const double *joints_dev, const int32_t *system_dev, const double *params_dev, int64_t n,
+                 int32_t max_pts, double *shape_dev, int32_t *npts_dev, int32_t *tip_idx_dev, double *tip_dev, void *stream);
+
 /* ---- hindsight replay on the device --------------------------------------------------------
  * Replaces what the reference delegates to stable_baselines' HER wrapper (third party, not vendored, version not
  * pinned: setup.py:5; call sites src/utils.py:5-7,27-28; settings saved_policies/.../config.yml: goal_selection_strategy

@@ -149,12 +149,22 @@ static double rms_scaled(const double *x, const double *scale) {
 
 typedef struct { int nfev, nacc, nrej; } cnt_t;
 
+/* backbone samples of one section (model.py:137-151: t_eval = np.linspace(span[k], span[k+1] - 1e-6, 30), values from scipy's
+ * RK45 dense output, rk.py RkDenseOutput._call_impl): te = the 30 abscissae, out = where the next sample's r goes */
+#define NEVAL 30
+typedef struct { double te[NEVAL]; int i; double *out; } shape_t;
+static shape_t *g_shape = 0;   /* set by ctr_oracle_fk_shape around its own dp45_section calls (single-threaded entry) */
+
 /* integrate one section from t0 to tf (tf >= t0); y updated in place; returns 0 ok, -1 step too small */
 static int dp45_section(const sec_t *c, double t0, double tf, double *y, double rtol, double atol, cnt_t *cnt) {
     double K[7][NY], ytmp[NY], ynew[NY], scale[NY], tmp[NY];
+    shape_t *sh = g_shape;
     rhs(c, y, K[0]);
     cnt->nfev += 1;
-    if (tf == t0) return 0;
+    if (tf == t0) {                                          /* ConstantDenseOutput: every sample is y0 (base.py) */
+        if (sh) for (; sh->i < NEVAL; ++sh->i) for (int d = 0; d < 3; ++d) sh->out[3 * sh->i + d] = y[6 + d];
+        return 0;
+    }
     /* select_initial_step (common.py:68-134) */
     double interval = fabs(tf - t0);
     for (int i = 0; i < NY; ++i) scale[i] = atol + fabs(y[i]) * rtol;
@@ -219,6 +229,23 @@ static int dp45_section(const sec_t *c, double t0, double tf, double *y, double 
             rejected = 1;
             cnt->nrej += 1;
         }
+        if (sh) {                                            /* ivp.py: t_eval points in (t_old, t_new] via searchsorted 'right' */
+            while (sh->i < NEVAL && sh->te[sh->i] <= t_new) {
+                const double x = (sh->te[sh->i] - t) / h;
+                double pw[4];
+                pw[0] = x; pw[1] = pw[0] * x; pw[2] = pw[1] * x; pw[3] = pw[2] * x;   /* np.cumprod */
+                for (int d = 0; d < 3; ++d) {
+                    double q = 0.0;
+                    for (int p = 0; p < 4; ++p) {
+                        double sq = 0.0;
+                        for (int j = 0; j < 7; ++j) sq += K[j][6 + d] * Pc[j][p];     /* Q = K.T.dot(P) */
+                        q += sq * pw[p];
+                    }
+                    sh->out[3 * sh->i + d] = h * q + y[6 + d];
+                }
+                sh->i += 1;
+            }
+        }
         if (t_new == tf) { /* stored sample at t_bound is the dense-output polynomial at x == 1 */
             for (int i = 0; i < NY; ++i) {
                 double q = 0.0;
@@ -263,6 +290,50 @@ int ctr_oracle_fk(const double *tc, const double *q, double rtol, double atol, d
     memcpy(out, y, sizeof y);
     if (info) { info[0] = cnt.nfev; info[1] = cnt.nacc; info[2] = cnt.nrej; info[3] = m; }
     return status;
+}
+
+/* backbone shape (model.py:66-68,137-172): r[npts][3] with npts = 30 x sections, tip_idx[3] = tip_pos (model.py:166-172).
+ * Not thread-safe (g_shape). Returns the number of points, or -1. */
+int ctr_oracle_fk_shape(const double *tc, const double *q, double rtol, double atol, double *r, int *tip_idx) {
+    double S[MAXSEC], EI[NT][MAXSEC], GJ[NT][MAXSEC], Ux[NT][MAXSEC], Uy[NT][MAXSEC];
+    int m = segment(tc, q, S, EI, GJ, Ux, Uy);
+    double y[NY], len[MAXSEC * NEVAL];
+    memset(y, 0, sizeof y);
+    y[3] = q[3]; y[4] = q[4]; y[5] = q[5];
+    double ca = cos(q[3]), sa = sin(q[3]);
+    y[9] = ca; y[10] = -sa; y[12] = sa; y[13] = ca; y[17] = 1.0;
+    cnt_t cnt = {0, 0, 0};
+    int status = 0;
+    double prev = 0.0;
+    shape_t sh;
+    for (int k = 0; k < m; ++k) {
+        sec_t c;
+        for (int i = 0; i < NT; ++i) { c.ei[i] = EI[i][k]; c.gj[i] = GJ[i][k]; c.ux0[i] = Ux[i][k]; c.uy0[i] = Uy[i][k]; }
+        const double a = prev, b = S[k] - 1e-6;              /* np.linspace(a, b, 30): i * step + a, last = b */
+        const double step = (b - a) / (NEVAL - 1);
+        for (int i = 0; i < NEVAL; ++i) sh.te[i] = (step == 0.0) ? ((double)i / (NEVAL - 1)) * (b - a) + a : (double)i * step + a;
+        sh.te[NEVAL - 1] = b;
+        if (b < a) {                                         /* model.py:145-148: np.sort(s_span) */
+            for (int i = 0; i < NEVAL / 2; ++i) { double z = sh.te[i]; sh.te[i] = sh.te[NEVAL - 1 - i]; sh.te[NEVAL - 1 - i] = z; }
+        }
+        for (int i = 0; i < NEVAL; ++i) len[k * NEVAL + i] = sh.te[i];
+        sh.i = 0;
+        sh.out = r + 3 * NEVAL * k;
+        double t0 = a, tf = b;
+        if (tf < t0) { double z = t0; t0 = tf; tf = z; }
+        g_shape = &sh;
+        if (dp45_section(&c, t0, tf, y, rtol, atol, &cnt)) status = -1;
+        g_shape = 0;
+        if (sh.i != NEVAL) status = -1;
+        prev = S[k];
+    }
+    for (int k = 0; k < NT; ++k) {                           /* model.py:166-172 */
+        const double d_tip = tc[k] + q[k];
+        int b = 0;
+        for (int i = 0; i < m * NEVAL; ++i) if (len[i] >= d_tip - 1e-3) { b = i; break; }
+        tip_idx[k] = b;
+    }
+    return status ? -1 : m * NEVAL;
 }
 
 /* per-section step attempts of one FK (analysis of the GPU kernel's lock-step cost, oracle/lockstep_sim.py):

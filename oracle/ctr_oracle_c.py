@@ -52,6 +52,19 @@ def fk_batch(tcs, joints, system=None, rtol=1e-3, atol=1e-6, nthreads=0):
     return dict(tip=state[:, 6:9].copy(), R=state[:, 9:18].copy(), state=state, info=info, failed=bad)
 
 
+def fk_shape(tc, q, rtol=1e-3, atol=1e-6):
+    """One configuration -> (r [npts][3], tip_idx [3]): Model.r and tip_pos of the reference (model.py:66-68,166-172)."""
+    r = np.zeros((270, 3))
+    tip = np.zeros(3, dtype=np.int32)
+    fn = lib().ctr_oracle_fk_shape
+    fn.restype = ctypes.c_int
+    n = fn(_p(np.ascontiguousarray(tc, dtype=np.float64)), _p(np.ascontiguousarray(q, dtype=np.float64)),
+           ctypes.c_double(rtol), ctypes.c_double(atol), _p(r), _p(tip))
+    if n < 0:
+        raise RuntimeError("ctr_oracle_fk_shape failed")
+    return r[:n].copy(), tip
+
+
 def segment(tc, beta):
     S = np.zeros(9)
     tab = np.zeros((4, 3, 9))

@@ -610,6 +610,45 @@ def test_host_step_entry_point_matches_device_path(vec_factory):
         assert torch.equal(envs[0].buffer(k), envs[1].buffer(k)), k
 
 
+def test_backbone_shape_vs_reference_and_oracle(golden, oracle_c, tube_constants, vec_factory):
+    """ctr_fk_shape against the reference's Model.r / tip_pos fixture: same number of samples, identical
+    split indices, positions within 1e-10 m (bar 1e-5 m); the last sample is the tip ctr_fk returns; r1/r2/r3 slice alike."""
+    g = golden('shape_reference')
+    env = vec_factory(16, select_systems=[0, 1, 2, 3])
+    q = g['joints'].astype(np.float64)
+    r, npts, tip_idx, tip = env.backbone_shape(q, system=g['system'])
+    r, npts, tip_idx, tip = r.cpu().numpy(), npts.cpu().numpy(), tip_idx.cpu().numpy(), tip.cpu().numpy()
+    assert np.array_equal(npts, g['npts']) and np.array_equal(tip_idx, g['tip_idx'])
+    mask = np.arange(270)[None, :] < npts[:, None]
+    assert np.abs(r - g['r'])[mask].max() < 1e-10
+    assert np.abs(tip - g['tip']).max() < 1e-10
+    tip_fk = env.forward_kinematics(q, system=g['system']).cpu().numpy()
+    assert np.array_equal(tip, tip_fk)                       # same integrator, same bits as ctr_fk
+    last = r[np.arange(len(npts)), npts - 1]
+    assert np.abs(last - tip).max() < 1e-13                  # dense output at x = 1 is y_new to round-off
+    for i in (0, 100, 333, 575):
+        r1, r2, r3 = env.split_backbone(r[i], npts[i], tip_idx[i])
+        t0, t1, t2 = g['tip_idx'][i]
+        ref = g['r'][i][:g['npts'][i]]
+        for mine, want in ((r1, ref[t1:t0 + 1]), (r2, ref[t2:t1 + 1]), (r3, ref[:t2 + 1])):
+            assert mine.shape == want.shape and (mine.size == 0 or np.abs(mine - want).max() < 1e-10)
+    # a truncating max_pts writes only what fits and still reports the full count
+    r60, n60, _, _ = env.backbone_shape(q[:32], system=g['system'][:32], max_pts=60)
+    assert np.array_equal(n60.cpu().numpy(), g['npts'][:32])
+    assert np.abs(r60.cpu().numpy()[:, :30] - g['r'][:32, :30]).max() < 1e-10
+    # random configurations of every system against the C oracle
+    rng = np.random.RandomState(5)
+    import ctr_oracle as O
+    for s in range(4):
+        qs = np.stack([O.sample_goal(rng, tube_constants[s][:3]) for _ in range(64)]).astype(np.float64)
+        rr, nn, ii, _ = env.backbone_shape(qs, system=np.full(64, s, dtype=np.int32))
+        rr, nn, ii = rr.cpu().numpy(), nn.cpu().numpy(), ii.cpu().numpy()
+        for k in range(64):
+            ro, io = oracle_c.fk_shape(tube_constants[s], qs[k])
+            assert nn[k] == len(ro) and np.array_equal(ii[k], io)
+            assert np.abs(rr[k, :nn[k]] - ro).max() < 1e-10
+
+
 def test_destroy_after_host_step_is_clean():
     """Regression: ctr_destroy freed the device staging buffer of ctr_step_host with cudaFreeHost; the 'invalid argument' stayed
     pending and failed the NEXT handle's first launch check (and leaked 24 B/env of device memory per handle)."""
