@@ -523,11 +523,11 @@ def extras(args, dev, pool):
     t.record()
     torch.cuda.synchronize(dev)
     us = s.elapsed_time(t) / 20 * 1e3
-    sample_bytes = 2 * (2 * D * 8 + 3 * 24 + 24 + 8 + 1) + 24 + 8 + 16        # gather in + batch out + donor goal + ring counters + src
+    sample_bytes = 2 * (2 * D * 8 + 3 * 24 + 24 + 8 + 1) + 24 + 8 + 16        # record in + batch out + donor goal + ring counters + src
     res["her_sample_2^20_future_k4"] = {"us_per_call": us, "transitions/s": m / (us * 1e-6), "GB/s": sample_bytes * m / (us * 1e-6) / 1e9,
                                         "bytes_per_transition": sample_bytes,
-                                        "bound": "hbm (gather: one 32-byte sector per 8-byte row element read)",
-                                        "ring_MB": cap * ENVS_PER_GPU * (2 * D * 8 + 3 * 24 + 24 + 8 + 1 + 8) / 1e6}
+                                        "bound": "hbm (gather of 352-byte records, a warp per 32 samples through shared memory)",
+                                        "ring_MB": cap * ENVS_PER_GPU * (352 + 9) / 1e6}
     e.close()
     return res
 

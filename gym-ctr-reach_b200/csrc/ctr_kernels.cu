@@ -1607,9 +1607,10 @@ static int her_check(const ctr_handle* h, const ctr_her_ring* r) {
     if (r->n_envs != h->n) CTR_FAIL("ring.n_envs differs from the handle's environment count");
     if (r->capacity < 1) CTR_FAIL("ring.capacity must be >= 1");
     if (r->obs_dim != h->obs_dim) CTR_FAIL("ring.obs_dim differs from ctr_obs_dim()");
-    if (!r->obs || !r->next_obs || !r->achieved || !r->next_achieved || !r->desired || !r->action || !r->reward ||
-        !r->done || !r->t_in_ep || !r->ep_len || !r->cur_obs || !r->cur_achieved || !r->cur_desired || !r->cur_t)
+    if (!r->rec || !r->done || !r->t_in_ep || !r->ep_len || !r->cur_obs || !r->cur_achieved || !r->cur_desired || !r->cur_t)
         CTR_FAIL("ring has a null buffer");
+    if (((uintptr_t)r->rec & 31) != 0) CTR_FAIL("ring.rec must be 32-byte aligned");
+    if (2 * r->obs_dim + 13 > CTR_HER_RECORD) CTR_FAIL("observation does not fit a replay record");
     return 0;
 }
 static HerSrc her_src(const ctr_handle* h) {
@@ -1642,8 +1643,8 @@ int ctr_her_store(ctr_handle* h, const ctr_her_ring* ring, const float* action_d
     if (!action_dev) CTR_FAIL("null action");
     if (slot < 0 || slot >= ring->capacity) CTR_FAIL("slot out of range");
     CTR_CUDA(cudaSetDevice(h->device));
-    k_her_store<<<(int)((h->n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(*ring, her_src(h), action_dev, stride_field,
-                                                                            stride_env, slot);
+    k_her_store<<<(int)((h->n + 32 * HER_WARPS - 1) / (32 * HER_WARPS)), 32 * HER_WARPS, 0, (cudaStream_t)stream>>>(
+        *ring, her_src(h), action_dev, stride_field, stride_env, slot);
     h->launches += 1;
     CTR_CUDA(cudaGetLastError());
     return 0;
@@ -1663,7 +1664,7 @@ int ctr_her_sample(ctr_handle* h, const ctr_her_ring* ring, int64_t n_stored, in
         CTR_FAIL("batch has a null buffer");
     CTR_CUDA(cudaSetDevice(h->device));
     if (tol < 0) tol = h->tol;
-    k_her_sample<<<(int)((b->m + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+    k_her_sample<<<(int)((b->m + 32 * HER_WARPS - 1) / (32 * HER_WARPS)), 32 * HER_WARPS, 0, (cudaStream_t)stream>>>(
         *ring, *b, n_stored, newest_slot, n_sampled_goal, rewrite_error, tol, h->cfg.reward_mode,
         make_uint2((unsigned)seed, (unsigned)(seed >> 32)), make_uint2((unsigned)call, (unsigned)(call >> 32)));
     h->launches += 1;

@@ -56,10 +56,12 @@ class CtrConfig(ctypes.Structure):
 
 
 class CtrHerRing(ctypes.Structure):
-    """ctr_her_ring (include/ctr_b200.h): caller-owned, time-major replay ring."""
+    """ctr_her_ring (include/ctr_b200.h): caller-owned, time-major, record-major replay ring."""
     _fields_ = [('n_envs', ctypes.c_int64), ('capacity', ctypes.c_int64), ('obs_dim', ctypes.c_int32), ('pad_', ctypes.c_int32)] + [
-        (k, ctypes.c_void_p) for k in ('obs', 'next_obs', 'achieved', 'next_achieved', 'desired', 'action', 'reward', 'done',
-                                       't_in_ep', 'ep_len', 'cur_obs', 'cur_achieved', 'cur_desired', 'cur_t')]
+        (k, ctypes.c_void_p) for k in ('rec', 'done', 't_in_ep', 'ep_len', 'cur_obs', 'cur_achieved', 'cur_desired', 'cur_t')]
+
+
+HER_RECORD = 44   # CTR_HER_RECORD: doubles per replay record
 
 
 class CtrHerBatch(ctypes.Structure):

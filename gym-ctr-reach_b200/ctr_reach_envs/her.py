@@ -19,9 +19,7 @@ from . import _lib
 KEY_ORDER_SB = ('observation', 'achieved_goal', 'desired_goal')
 KEY_ORDER_REFERENCE_TESTS = ('observation', 'desired_goal', 'achieved_goal')
 
-_RING = (('obs', 'D', torch.float64), ('next_obs', 'D', torch.float64), ('achieved', 3, torch.float64),
-         ('next_achieved', 3, torch.float64), ('desired', 3, torch.float64), ('action', 6, torch.float32),
-         ('reward', 0, torch.float64), ('done', 0, torch.uint8), ('t_in_ep', 0, torch.int32), ('ep_len', 0, torch.int32))
+_RING_INTS = (('done', torch.uint8), ('t_in_ep', torch.int32), ('ep_len', torch.int32))
 _BATCH = (('obs', 'D', torch.float64), ('next_obs', 'D', torch.float64), ('achieved', 3, torch.float64),
           ('next_achieved', 3, torch.float64), ('desired', 3, torch.float64), ('action', 6, torch.float32),
           ('reward', 0, torch.float64), ('done', 0, torch.uint8), ('src', 0, torch.int64), ('goal_src', 0, torch.int64))
@@ -40,9 +38,10 @@ class HerReplay(object):
         self.flat_order = tuple(flat_order)
         assert sorted(self.flat_order) == sorted(KEY_ORDER_SB)
         N, D, dev = env.num_envs, env.obs_dim, env.device
-        rows = lambda r: D if r == 'D' else r
-        self.ring = {k: torch.zeros(((rows(r), self.capacity * N) if r else (self.capacity * N,)), dtype=dt, device=dev)
-                     for k, r, dt in _RING}
+        # record major: transition (slot, env) = row slot * N + env of `rec`, 44 doubles = 352 B = 11 aligned sectors
+        # (include/ctr_b200.h gives the field offsets), so that a sample gathers whole sectors
+        self.ring = {'rec': torch.zeros((self.capacity * N, _lib.HER_RECORD), dtype=torch.float64, device=dev)}
+        self.ring.update({k: torch.zeros(self.capacity * N, dtype=dt, device=dev) for k, dt in _RING_INTS})
         self.ring.update(cur_obs=torch.zeros((D, N), dtype=torch.float64, device=dev),
                          cur_achieved=torch.zeros((3, N), dtype=torch.float64, device=dev),
                          cur_desired=torch.zeros((3, N), dtype=torch.float64, device=dev),
@@ -50,6 +49,16 @@ class HerReplay(object):
         self._c = _lib.CtrHerRing(n_envs=N, capacity=self.capacity, obs_dim=D, pad_=0,
                                   **{k: v.data_ptr() for k, v in self.ring.items()})
         self.stored, self.newest, self.calls = 0, -1, 0
+
+    def records(self):
+        """Decoded view of the ring for inspection / checkpointing: dict of (capacity, N, ...) tensors."""
+        N, D, c = self.env.num_envs, self.env.obs_dim, self.capacity
+        rec = self.ring['rec'].reshape(c, N, _lib.HER_RECORD)
+        out = dict(obs=rec[..., :D], next_obs=rec[..., D:2 * D], achieved=rec[..., 2 * D:2 * D + 3],
+                   next_achieved=rec[..., 2 * D + 3:2 * D + 6], desired=rec[..., 2 * D + 6:2 * D + 9], reward=rec[..., 2 * D + 9],
+                   action=rec[..., 2 * D + 10:2 * D + 13].contiguous().view(torch.float32))
+        out.update({k: self.ring[k].reshape(c, N) for k, _ in _RING_INTS})
+        return out
 
     def begin(self):
         """Call after env.reset(): the next stored transition starts from the env's current observation."""

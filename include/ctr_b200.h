@@ -196,16 +196,18 @@ int ctr_fk_shape(ctr_handle *h, const double *joints_dev, const int32_t *system_
  * Replaces what the reference delegates to stable_baselines' HER wrapper (third party, not vendored, version not
  * pinned: setup.py:5; call sites src/utils.py:5-7,27-28; settings saved_policies/.../config.yml: goal_selection_strategy
  * future, n_sampled_goal 4, buffer_size 500000, batch_size 256).  The relabelled reward is the reference's own
- * compute_reward (ctr_reach_env.py:160-170).  The ring is CALLER-OWNED device memory, time major: transition
- * (slot, env) lives at column slot * n_envs + env of every SoA row, rows are capacity * n_envs apart. */
+ * compute_reward (ctr_reach_env.py:160-170).  The ring is CALLER-OWNED device memory, time major and RECORD major:
+ * transition (slot, env) is record number slot * n_envs + env; a record is CTR_HER_RECORD doubles (352 bytes = 11 aligned
+ * 32-byte sectors), so that sampling -- a gather of random records -- moves whole sectors:
+ *   [0, D) obs | [D, 2D) next_obs | 2D + 0..2 achieved | 2D + 3..5 next_achieved | 2D + 6..8 desired | 2D + 9 reward |
+ *   2D + 10..12 action (6 x f32 packed in 3 doubles) | padding.
+ * The few integers the index arithmetic needs before it touches a record stay in separate arrays. */
+#define CTR_HER_RECORD 44
 typedef struct {
     int64_t n_envs, capacity;      /* capacity = number of step slots                                            */
     int32_t obs_dim;               /* D = ctr_obs_dim()                                                          */
     int32_t pad_;
-    double *obs, *next_obs;        /* f64 [D][capacity*n]  'observation' before / after the step                 */
-    double *achieved, *next_achieved, *desired;   /* f64 [3][capacity*n]                                         */
-    float *action;                 /* f32 [6][capacity*n]                                                        */
-    double *reward;                /* f64 [capacity*n]                                                           */
+    double *rec;                   /* f64 [capacity*n][CTR_HER_RECORD], 32-byte aligned                          */
     uint8_t *done;                 /* u8  [capacity*n]                                                           */
     int32_t *t_in_ep;              /* i32 [capacity*n]  1-based index of the transition inside its episode        */
     int32_t *ep_len;               /* i32 [capacity*n]  length of its episode; 0 while the episode is still open  */

@@ -120,8 +120,7 @@ def _rollout_both(vec_factory, n, cap, steps, tol, **kw):
 
 
 def _ring_dev(rep, key, n, cap):
-    t = rep.ring[key].cpu().numpy()
-    return t.reshape(t.shape[0], cap, n).transpose(1, 2, 0) if t.ndim == 2 else t.reshape(cap, n)
+    return rep.records()[key].cpu().numpy()          # (capacity, N, ...) decoded from the record-major ring
 
 
 @pytest.mark.gpu
