@@ -812,7 +812,10 @@ __global__ void __launch_bounds__(256) k_fma_peak(T* out, int iters, T b, T c) {
 }  // namespace
 
 // ================================================================================================================
-constexpr int N_COMPUTE_STREAMS = 4;
+#ifndef CTR_COMPUTE_STREAMS
+#define CTR_COMPUTE_STREAMS 4
+#endif
+constexpr int N_COMPUTE_STREAMS = CTR_COMPUTE_STREAMS;   // ctr_step_host: chunk kernels round-robin over this many streams
 
 struct HostGraph {              // one captured ctr_step_host pipeline (keyed by the caller's host pointers)
     const void* key[8];
