@@ -649,6 +649,82 @@ def test_backbone_shape_vs_reference_and_oracle(golden, oracle_c, tube_constants
             assert np.abs(rr[k, :nn[k]] - ro).max() < 1e-10
 
 
+def test_full_size_step_properties(oracle_c, tube_constants, vec_factory):
+    """BASELINE.json config 3 at its full size on ONE GPU (2^20 environments, sparse reward, auto-reset): invariants that do
+    not need an oracle run of that size -- constraint predicates, flags recomputed from the buffers, observation consistency,
+    shard invariance against a small handle at the same global offset -- plus the C oracle on a 20000-env sample."""
+    N, tol = 1 << 20, 0.02
+    env = vec_factory(N, seed=9)
+    env.goal_tolerance.current_tol = tol
+    env.reset()
+    k0, nk = 777 * 640, 4096
+    small = vec_factory(nk, seed=9, env_offset=k0)
+    small.goal_tolerance.current_tol = tol
+    small.reset()
+    g = torch.Generator(device='cuda')
+    g.manual_seed(21)
+    lim = torch.tensor(env.action_space.high, device='cuda')
+    sc = tube_constants[0]
+    L = torch.tensor(sc[:3], dtype=torch.float64, device='cuda')
+    low = (-L + 1e-3).to(torch.float32)
+    d10 = torch.tensor(np.float32(float(sc[1]) - float(sc[0])), device='cuda')
+    d21 = torch.tensor(np.float32(float(sc[2]) - float(sc[1])), device='cuda')
+    Lf = L.to(torch.float32)
+    finished = 0
+    for step in range(4):
+        act = ((torch.rand((N, 6), device='cuda', generator=g) * 2 - 1) * lim).contiguous()
+        des_before = env.buffer('desired_goal').clone()
+        t_before = env.buffer('t').clone()
+        q_before = env.buffer('joints').t().cpu().numpy().copy()
+        obs, reward, done, info = env.step(act)
+        small.step(act[k0:k0 + nk].contiguous())
+        torch.cuda.synchronize()
+        q = env.buffer('joints')                                   # f32 [6][N]; finished envs already hold the new start joints
+        b0, b1, b2 = q[0], q[1], q[2]
+        dn = done.bool()
+        # box limits always hold.  Obs.set_action applies its ordering constraints SEQUENTIALLY (obs.py:176-183: beta_0 is fixed up
+        # against beta_1 before beta_1 is lowered against beta_2), so after a step only the last pair is an invariant -- the
+        # reference can leave beta_0 > beta_1, and so must this kernel.  Freshly sampled episodes satisfy all of sample_goal's
+        # predicates (obs.py:198-200).
+        assert bool(((q[:3] >= low[:, None]) & (q[:3] <= 0)).all())
+        assert bool(((b1 <= b2) & (b1 >= d21 + b2))[~dn].all())
+        assert bool(((b0 <= b1) & (b1 <= b2) & (b0 + Lf[0] >= Lf[1] + b1) & (b1 + Lf[1] >= Lf[2] + b2))[dn].all())
+        # every environment's constraint arithmetic against the C oracle (pinned to the reference's set_action traces), bit for bit
+        want = oracle_c.set_action_batch(q_before, act.cpu().numpy(), None, [sc[:3]], False, 10)
+        keep = (~dn).cpu().numpy()
+        assert np.array_equal(q.t().cpu().numpy()[keep], want[keep])
+        # error / reward / success / done recomputed from the buffers, bit for bit (ctr_reach_env.py:140,155-170)
+        ach = torch.where(dn[None, :], env.buffer('terminal_achieved'), env.buffer('achieved_goal'))
+        diff = ach - des_before
+        sq = diff * diff
+        err = torch.sqrt((sq[0] + sq[1]) + sq[2])
+        assert torch.equal(err, info['error'])
+        assert torch.equal(reward, -(err > tol).double()) and torch.equal(torch.signbit(reward), torch.signbit(-(err > tol).double()))
+        assert torch.equal(info['is_success'].bool(), err < tol)
+        assert torch.equal(dn, (~(err > tol)) | (t_before + 1 >= 150))
+        assert torch.equal(env.buffer('t'), torch.where(dn, torch.zeros_like(t_before), t_before + 1))
+        finished += int(dn.sum())
+        # observation of the state the env is in now (obs.py:136-164, egocentric): trig pairs, first differences, error, tol
+        o = env.buffer('observation')
+        qd = q.double()
+        assert torch.equal(o[2], qd[0]) and torch.equal(o[5], qd[1] - qd[0]) and torch.equal(o[8], qd[2] - qd[1])
+        for j in range(3):
+            assert float((o[3 * j] ** 2 + o[3 * j + 1] ** 2 - 1).abs().max()) < 1e-14
+        assert torch.equal(o[9:12], env.buffer('desired_goal') - env.buffer('achieved_goal'))
+        assert bool((o[12] == tol).all())
+        # the envs [k0, k0 + nk) of the big job are the small job, bit for bit
+        for name in ('joints', 'achieved_goal', 'desired_goal', 'observation', 'reward', 'done', 'error', 't'):
+            assert torch.equal(env.buffer(name)[..., k0:k0 + nk], small.buffer(name)), name
+    assert finished > 0                                            # the auto-reset path ran at this size
+    idx = torch.randperm(N, device='cuda', generator=g)[:20000]
+    qs = env.buffer('joints').t()[idx].double()
+    tip = env.forward_kinematics(qs).cpu().numpy()
+    ref = oracle_c.fk_batch(tube_constants[:1], qs.cpu().numpy(), None, nthreads=8)
+    assert np.abs(tip - ref['tip']).max() < 1e-10
+    st = env.stats()
+    assert st['env_steps'] == 4.0 * N and st['episodes'] == finished
+
+
 def test_destroy_after_host_step_is_clean():
     """Regression: ctr_destroy freed the device staging buffer of ctr_step_host with cudaFreeHost; the 'invalid argument' stayed
     pending and failed the NEXT handle's first launch check (and leaked 24 B/env of device memory per handle)."""
