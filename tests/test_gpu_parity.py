@@ -725,6 +725,35 @@ def test_full_size_step_properties(oracle_c, tube_constants, vec_factory):
     assert st['env_steps'] == 4.0 * N and st['episodes'] == finished
 
 
+def test_evaluation_frame_from_vec_env(oracle_c, tube_constants, vec_factory, tmp_path):
+    """evaluation.evaluate: one row per finished episode in the reference's CSV layout; every row is
+    re-derived with the C oracle (achieved / desired / starting tips are the FK of the row's own joints)."""
+    from ctr_reach_envs import evaluation as E
+    env = vec_factory(512, auto_reset=False, evaluation=True, seed=3, **ALL4)
+    env.goal_tolerance.current_tol = 0.03
+    g = torch.Generator(device='cuda')
+    g.manual_seed(1)
+    lim = torch.tensor(env.action_space.high, device='cuda')
+    policy = lambda obs: ((torch.rand((512, 6), device='cuda', generator=g) * 2 - 1) * lim).contiguous()
+    df = E.evaluate(env, policy, 700, max_steps=40)
+    assert list(df.columns) == E.EVAL_COLUMNS and len(df) == 700
+    sysid = df['system_id'].to_numpy().astype(np.int32)
+    assert set(np.unique(sysid)) <= {0, 1, 2, 3} and len(np.unique(sysid)) == 4
+    assert df['episode_length'].between(1, 40).all()
+    col = lambda *names: df[list(names)].to_numpy()
+    for which, goal in (('achieved', ('achieved_goal_x', 'achieved_goal_y', 'achieved_goal_z')),
+                        ('desired', ('desired_goal_x', 'desired_goal_y', 'desired_goal_z')),
+                        ('starting', ('starting_position_x', 'starting_position_y', 'starting_position_z'))):
+        q = np.concatenate((col(*['B_%s_%d' % (which, i) for i in (1, 2, 3)]), col(*['alpha_%s_%d' % (which, i) for i in (1, 2, 3)])), axis=1)
+        assert np.array_equal(q, q.astype(np.float32).astype(np.float64))          # float32 joints widened, as in the reference's files
+        ref = oracle_c.fk_batch(tube_constants, q, sysid)
+        assert np.abs(ref['tip'] - col(*goal)).max() < 1e-10, which
+    path = tmp_path / 'ev.csv'
+    E.write_evaluations(str(path), df)
+    back = E.read_evaluations(str(path))
+    assert np.array_equal(back.to_numpy(), df.to_numpy())                           # round_trip parsing: the same doubles
+
+
 def test_destroy_after_host_step_is_clean():
     """Regression: ctr_destroy freed the device staging buffer of ctr_step_host with cudaFreeHost; the 'invalid argument' stayed
     pending and failed the NEXT handle's first launch check (and leaked 24 B/env of device memory per handle)."""

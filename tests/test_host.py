@@ -146,3 +146,23 @@ def test_shard_range_partitions(lib):
         sizes = [hi - lo for lo, hi in spans]
         assert max(sizes) - min(sizes) <= 1
     assert shard_range(1 << 20, 3, 8) == (3 * 131072, 4 * 131072)
+
+
+def test_evaluation_csv_round_trip(tmp_path):
+    """The reference's evaluation files (src/rotation_evaluation.py:66-81) read and written back byte for byte; the fixture is
+    the head of a file the reference ships (oracle/make_golden_csv.py)."""
+    from ctr_reach_envs import evaluation as E
+    src = os.path.join(ROOT, 'tests', 'golden', 'evaluations_sample.csv')
+    df = E.read_evaluations(src)
+    assert list(df.columns) == E.EVAL_COLUMNS and df.shape == (25, 29)
+    out = tmp_path / 'evaluations.csv'
+    E.write_evaluations(str(out), df)
+    assert out.read_text() == open(src).read()
+    # make_frame stacks in the reference's column order (rotation_evaluation.py:66-68)
+    q = np.arange(12, dtype=np.float32).reshape(2, 6)
+    f = E.make_frame(np.zeros((2, 3)), np.ones((2, 3)), [5, 6], np.full((2, 3), 2.0), q, q + 100, q + 200, [0, 3])
+    assert f['B_desired_2'].tolist() == [1.0, 7.0] and f['alpha_achieved_1'].tolist() == [103.0, 109.0]
+    assert f['alpha_starting_3'].tolist() == [205.0, 211.0] and f['episode_length'].tolist() == [5.0, 6.0]
+    assert f['system_id'].tolist() == [0.0, 3.0]
+    with pytest.raises(ValueError):
+        E.write_evaluations(str(out), f.drop(columns=['system_id']))
