@@ -385,6 +385,8 @@ def gpu_arm(args):
             except Exception as exc:  # pragma: no cover
                 line["cpu_baseline"]["c_port"] = {"error": str(exc)}
             line["tip_error_m"] = tip_error_check(env)
+        if world == 1 and not args.no_kernel_table:
+            line["kernels"] = kernel_table(args, dev, pool, peak, hbm_peak)
         if world == 1 and args.extras:
             line["extra"] = extras(args, dev, pool)
     env.close()
@@ -415,6 +417,102 @@ def tip_error_check(env):
     ref = C.fk_batch(C.derive(O.DEFAULT_SYSTEMS[:1]), q, None, nthreads=host_cores())
     e = np.linalg.norm(tip - ref['tip'], axis=1)
     return {"n": int(n), "max": float(e.max()), "mean": float(e.mean()), "vs": "C oracle (scipy-RK45 restatement)"}
+
+
+def kernel_table(args, dev, pool, fma_peak, hbm_peak):
+    """Roofline fraction of EVERY kernel of the library at the bench's size (131072 envs / 2^20 transitions), one GPU: CUDA events
+    around back-to-back launches after warm-up; algorithmic flops from the integrator's own counters (nfev*120 +
+    attempts*1290 + sections*200), algorithmic bytes from the rows a thread reads and writes.  k_step is in `roofline`."""
+    import ctypes
+    import numpy as np
+    import torch
+    import ctr_reach_envs
+    from ctr_reach_envs import _lib
+    from ctr_reach_envs.envs import CtrReachVecEnv
+    from ctr_reach_envs.her import HerReplay
+    N, tab = ENVS_PER_GPU, {}
+    k = ctr_reach_envs.default_kwargs()
+    e = CtrReachVecEnv(N, device=dev.index, **k)
+    e.goal_tolerance.current_tol = args.tol
+    e.reset()
+    lib, h, st = e.lib, e.handle, e._stream()
+
+    def timed(fn, reps=10, warm=2):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize(dev)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize(dev)
+        return a.elapsed_time(b) / reps * 1e-3
+
+    def fma_row(name, sec, flop, note=""):
+        tab[name] = {"bound": "fma", "us": sec * 1e6, "achieved": flop / sec / 1e12, "peak": fma_peak, "unit": "TFLOP/s",
+                     "frac": flop / sec / 1e12 / fma_peak, "note": note}
+
+    def hbm_row(name, sec, nbytes, note=""):
+        tab[name] = {"bound": "hbm", "us": sec * 1e6, "achieved": nbytes / sec / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": nbytes / sec / 1e9 / hbm_peak, "note": note}
+
+    # ---- k_fk<f64,dp45>: Model.forward_kinematics on the envs' own joints
+    q = e.buffer('joints').to(torch.float64).contiguous()                  # [6][N]
+    tip = torch.empty((3, N), dtype=torch.float64, device=dev)
+    R = torch.empty((9, N), dtype=torch.float64, device=dev)
+    info = torch.empty((4, N), dtype=torch.int32, device=dev)
+    fk = lambda: _lib.check(lib.ctr_fk(h, _lib.ptr(q), None, None, N, -1, -1, _lib.ptr(tip), _lib.ptr(R), _lib.ptr(info), st))
+    sec = timed(fk)
+    inf = info.double().sum(dim=1).tolist()                                # nfev, accepted, rejected, sections
+    fk_flop = inf[0] * F_RHS + (inf[1] + inf[2]) * F_STEP + inf[3] * F_SECTION
+    fma_row("k_fk<f64,dp45>", sec, fk_flop, "131072 configs")
+    # ---- k_fk_shape: the same solves + 30 dense-output samples per section
+    shape = torch.empty((N, 270, 3), dtype=torch.float64, device=dev)
+    npts = torch.empty(N, dtype=torch.int32, device=dev)
+    tidx = torch.empty((3, N), dtype=torch.int32, device=dev)
+    sec = timed(lambda: _lib.check(lib.ctr_fk_shape(h, _lib.ptr(q), None, None, N, 270, _lib.ptr(shape), _lib.ptr(npts), _lib.ptr(tidx),
+                                                    _lib.ptr(tip), st)))
+    pts = float(npts.double().sum())
+    fma_row("k_fk_shape", sec, fk_flop + pts * 3 * 12.0, "131072 configs; + 12 flop per sample and component; writes %.0f MB" % (pts * 24 / 1e6))
+    # ---- k_reset: CtrReachEnv.reset of every env = 2 FK solves + goal sampling
+    def full_reset():
+        _lib.check(lib.ctr_reset(h, None, None, None, st))
+    e.stats_reset()
+    sec = timed(full_reset, reps=4, warm=1)
+    w = e.work_counters()
+    fma_row("k_reset<f64,dp45>", sec, (w['nfev'] * F_RHS + w['attempts'] * F_STEP + w['sections'] * F_SECTION) / 5.0,
+            "131072 envs, 2 FK each (5 envs per warp: half the lanes of k_step per solve)")
+    # ---- k_set_action: the constraint op alone (48 B in, 24 B out per env)
+    act = pool[0].t().contiguous()
+    jj = e.buffer('joints').clone()
+    sec = timed(lambda: _lib.check(lib.ctr_set_action(h, _lib.ptr(jj), _lib.ptr(act), None, N, 10, st)), reps=20)
+    hbm_row("k_set_action", sec, 72.0 * N, "131072 envs: 9.4 MB, launch-latency sized")
+    # ---- k_reward: compute_reward + obs[9:12] rewrite on 2^20 transitions (config 4), 80 B each; the 84 MB set is L2 resident
+    m = 1 << 20
+    a3 = torch.rand((3, m), dtype=torch.float64, device=dev)
+    d3 = a3[:, torch.randperm(m, device=dev)].contiguous()
+    rew = torch.empty(m, dtype=torch.float64, device=dev)
+    ob = torch.zeros((13, m), dtype=torch.float64, device=dev)
+    sec = timed(lambda: e.compute_reward_soa(a3, d3, rew, obs=ob, tol=0.001), reps=30, warm=3)
+    hbm_row("k_reward (relabel)", sec, 80.0 * m, "2^20 transitions back to back: L2 resident, can exceed the HBM figure")
+    # ---- hindsight replay: store one step of 131072 envs, sample 2^20 transitions ('future', k = 4)
+    D, cap = e.obs_dim, 16
+    rep = HerReplay(e, cap, n_sampled_goal=4, seed=1)
+    rep.begin()
+    for i in range(cap + 2):
+        e.step(pool[i % 4])
+        rep.store(pool[i % 4])
+    sec = timed(lambda: rep.store(pool[0]), reps=20)
+    hbm_row("k_her_store", sec, (3 * D * 8 + 2 * D * 8 + 6 * 24 + 24 + 8 + 1 + 352 + 16.0) * N,
+            "131072 envs: obs / terminal / cur rows in, cur rows + one 352-byte record out")
+    batch = rep.alloc_batch(m)
+    calls = iter(range(1000))
+    sec = timed(lambda: rep.sample(m, out=batch, call=next(calls)), reps=20, warm=3)
+    hbm_row("k_her_sample", sec, (352 + 24 + 12 + 2 * D * 8 + 3 * 24 + 24 + 8 + 1 + 16.0) * m,
+            "2^20 samples from a %.0f MB ring: one record + donor goal + 3 counters in, the batch rows out" % (cap * N * 361 / 1e6))
+    e.close()
+    return tab
 
 
 def extras(args, dev, pool):
@@ -545,6 +643,7 @@ def main():
     ap.add_argument('--rk4-steps', type=int, default=8)
     ap.add_argument('--cpu-steps', type=int, default=1500, help='timed steps of the CPU port per process (2 envs each): ~12 s on 16 cores')
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--no-kernel-table', action='store_true', help='skip the per-kernel roofline table (1 GPU)')
     ap.add_argument('--extras', action='store_true', help='also time the other BASELINE.json configs (1 GPU)')
     args = ap.parse_args()
     claim_stdout()

@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk(const SysConst* __rest
 
 // Backbone shape: Model.r and tip_pos of the reference (model.py:66-68,137-172) -- 30 samples per
 // section from the integrator's dense output, and for every tube the first sample index whose abscissa reaches
-// L_k + beta_k - 1e-3 (the split points of r1 / r2 / r3).  shape f64 [3][max_pts][n], npts i32 [n], tip_idx i32 [3][n].
+// L_k + beta_k - 1e-3 (the split points of r1 / r2 / r3).  shape f64 [n][max_pts][3], npts i32 [n], tip_idx i32 [3][n].
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk_shape(const SysConst* __restrict__ sys, int n_systems,
                                                     const double* __restrict__ joints, const int32_t* __restrict__ system,
                                                     const double* __restrict__ params, int64_t n, double rtol, double atol,
@@ -266,8 +266,8 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk_shape(const SysConst* 
     double y[6];
     FkInfo info;
     ShapeOut so;
-    so.base = shape + ((int64_t)id.j * max_pts) * n + e;
-    so.stride = n;
+    so.base = shape + (e * max_pts) * 3 + id.j;      // [n][max_pts][3]: an env's polyline is contiguous, its 3 lanes write 24 B
+    so.stride = 3;
     so.max_pts = valid ? max_pts : 0;
     fk_group_shape(id, valid, gs, LL, LL + 3, der, beta, alpha, rtol, atol, y, info, so);
     if (valid) {

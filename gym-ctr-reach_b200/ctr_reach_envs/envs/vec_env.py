@@ -246,13 +246,13 @@ class CtrReachVecEnv(object):
         q = torch.as_tensor(joints, dtype=torch.float64, device=self.device).reshape(-1, 6).t().contiguous()
         n = q.shape[1]
         s = None if system is None else torch.as_tensor(system, dtype=torch.int32, device=self.device).expand(n).contiguous()
-        shape = torch.zeros((3, max_pts, n), dtype=torch.float64, device=self.device)
+        shape = torch.zeros((n, max_pts, 3), dtype=torch.float64, device=self.device)
         npts = torch.empty(n, dtype=torch.int32, device=self.device)
         tip_idx = torch.empty((3, n), dtype=torch.int32, device=self.device)
         tip = torch.empty((3, n), dtype=torch.float64, device=self.device)
         _lib.check(self.lib.ctr_fk_shape(self.handle, _lib.ptr(q), _lib.ptr(s), None, n, int(max_pts), _lib.ptr(shape),
                                          _lib.ptr(npts), _lib.ptr(tip_idx), _lib.ptr(tip), self._stream()))
-        return shape.permute(2, 1, 0), npts, tip_idx.t(), tip.t()
+        return shape, npts, tip_idx.t(), tip.t()
 
     @staticmethod
     def split_backbone(r, npts, tip_idx):

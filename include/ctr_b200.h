@@ -186,7 +186,9 @@ int64_t ctr_launch_count(const ctr_handle *h);
  * (solve_ivp's t_eval = np.linspace(span[k], span[k+1] - 1e-6, 30), scipy RK45 dense output) and, per tube, the index of
  * the first sample at or beyond L_k + beta_k - 1e-3, which splits r into r1 = r[tip1 : tip0 + 1], r2 = r[tip2 : tip1 + 1],
  * r3 = r[: tip2 + 1].  Replaces the data the matplotlib renderer (envs/ctr_3d_graph.py) and src/utils.py:52-54 consume.
- * joints f64 [6][n] -> shape f64 [3][max_pts][n] (samples past npts are left untouched), npts i32 [n] (30 x sections),
+ * joints f64 [6][n] -> shape f64 [n][max_pts][3] (one contiguous polyline per configuration -- the one array of this
+ * ABI that is not SoA: the consumers want r[i] as (npts, 3), and the writes of an env land in consecutive sectors; samples
+ * past npts are left untouched), npts i32 [n] (30 x sections),
  * tip_idx i32 [3][n], tip f64 [3][n] or NULL.  Always the float64 scipy-RK45 parity integrator.  A section table can hold
  * 9 sections: max_pts = 270 never truncates. */
 int ctr_fk_shape(ctr_handle *h, const double *joints_dev, const int32_t *system_dev, const double *params_dev, int64_t n,
