@@ -20,6 +20,7 @@
 #include "../../include/ctr_b200.h"
 #include "ctr_device.cuh"
 #include "ctr_her.cuh"
+#include "ctr_ik.cuh"
 
 using namespace ctr;
 
@@ -863,6 +864,8 @@ struct ctr_handle {
     float* stage_action;
     int64_t stage_fk_cap;
     void* stage_fk_dev;
+    int64_t ik_cap;            // ctr_jacobian / ctr_ik_dls scratch: joints f64 [6][7n] | tips f64 [3][7n] | system i32 [7n] | frozen u8 [n] | active i32
+    void* ik_dev;
 };
 
 namespace {
@@ -1025,6 +1028,8 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     h->stage_action = nullptr;
     h->stage_fk_cap = 0;
     h->stage_fk_dev = nullptr;
+    h->ik_cap = 0;
+    h->ik_dev = nullptr;
     cudaDeviceProp prop;
     CTR_CUDA(cudaGetDeviceProperties(&prop, device));
     h->sm_count = prop.multiProcessorCount;
@@ -1139,6 +1144,7 @@ int ctr_destroy(ctr_handle* h) {
     for (void* ptr : h->allocs) cudaFree(ptr);
     if (h->stage_action) cudaFree(h->stage_action);      // device staging of ctr_step_host (cudaMalloc, step_host_impl)
     if (h->stage_fk_dev) cudaFree(h->stage_fk_dev);
+    if (h->ik_dev) cudaFree(h->ik_dev);
     if (h->stream) cudaStreamDestroy(h->stream);
     for (int k = 1; k <= N_COMPUTE_STREAMS; ++k) {
         if (h->streams[k]) cudaStreamDestroy(h->streams[k]);
@@ -1687,6 +1693,97 @@ int ctr_fk_shape(ctr_handle* h, const double* joints_dev, const int32_t* system_
                                                                tip_idx_dev, tip_dev, h->p.stats);
     h->launches += 1;
     CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---- finite-difference Jacobian / DLS inverse kinematics (kernels in ctr_ik.cuh) ----------------------
+struct IkScratch {
+    double* block;     // f64 [6][7n]
+    double* tips;      // f64 [3][7n]
+    int32_t* system;   // i32 [7n]
+    int32_t* active;   // i32 [1]
+    uint8_t* frozen;   // u8  [n]
+};
+static int ik_scratch(ctr_handle* h, int64_t n, IkScratch* out) {
+    if (h->ik_cap < n) {
+        if (h->ik_dev) CTR_CUDA(cudaFree(h->ik_dev));
+        h->ik_dev = nullptr;
+        h->ik_cap = 0;
+        CTR_CUDA(cudaMalloc(&h->ik_dev, (size_t)n * (7 * 6 * 8 + 7 * 3 * 8 + 7 * 4 + 1) + 64));
+        h->ik_cap = n;
+    }
+    const int64_t c = h->ik_cap;
+    out->block = (double*)h->ik_dev;
+    out->tips = out->block + 42 * c;
+    out->system = (int32_t*)(out->tips + 21 * c);
+    out->active = out->system + 7 * c;
+    out->frozen = (uint8_t*)(out->active + 16);
+    return 0;
+}
+// the 7n kinematics solves of one Jacobian: unperturbed + one column block per joint
+static int ik_solve7(ctr_handle* h, const IkScratch& sc, const double* q_dev, const int32_t* system_dev, int64_t n, double eps,
+                     cudaStream_t st) {
+    k_ik_perturb<<<(int)((n + 255) / 256), 256, 0, st>>>(q_dev, n, eps, sc.block);
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return ctr_fk(h, sc.block, system_dev ? sc.system : nullptr, nullptr, 7 * n, CTR_INTEGRATOR_DP45, CTR_PRECISION_F64, sc.tips,
+                  nullptr, nullptr, st);
+}
+static int ik_systems(const IkScratch& sc, const int32_t* system_dev, int64_t n, cudaStream_t st) {
+    if (!system_dev) return 0;
+    for (int k = 0; k < 7; ++k)
+        CTR_CUDA(cudaMemcpyAsync(sc.system + (int64_t)k * n, system_dev, sizeof(int32_t) * n, cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+
+int ctr_jacobian(ctr_handle* h, const double* joints_dev, const int32_t* system_dev, int64_t n, double eps, double* J_dev,
+                 double* tip_dev, void* stream) {
+    if (!h || !joints_dev || !J_dev) CTR_FAIL("null argument");
+    if (!(eps > 0.0)) CTR_FAIL("eps must be > 0");
+    if (n <= 0) return 0;
+    CTR_CUDA(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    IkScratch sc;
+    int rc = ik_scratch(h, n, &sc);
+    if (!rc) rc = ik_systems(sc, system_dev, n, st);
+    if (!rc) rc = ik_solve7(h, sc, joints_dev, system_dev, n, eps, st);
+    if (rc) return rc;
+    k_ik_jacobian<<<(int)((n + 255) / 256), 256, 0, st>>>(sc.tips, n, eps, J_dev, tip_dev);
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int ctr_ik_dls(ctr_handle* h, const double* target_dev, double* joints_dev, const int32_t* system_dev, int64_t n, double lam,
+               double eps, double tol, int32_t max_iters, double* err_dev, int32_t* iters_dev, void* stream) {
+    if (!h || !target_dev || !joints_dev || !err_dev || !iters_dev) CTR_FAIL("null argument");
+    if (!(eps > 0.0) || !(lam >= 0.0) || max_iters < 0) CTR_FAIL("bad eps / lam / max_iters");
+    if (n <= 0) return 0;
+    CTR_CUDA(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    IkScratch sc;
+    int rc = ik_scratch(h, n, &sc);
+    if (!rc) rc = ik_systems(sc, system_dev, n, st);
+    if (rc) return rc;
+    CTR_CUDA(cudaMemsetAsync(sc.frozen, 0, (size_t)n, st));
+    CTR_CUDA(cudaMemsetAsync(iters_dev, 0, sizeof(int32_t) * n, st));
+    CTR_CUDA(cudaMemsetAsync(err_dev, 0, sizeof(double) * n, st));
+    for (int it = 0; it < max_iters; ++it) {
+        CTR_CUDA(cudaMemsetAsync(sc.active, 0, sizeof(int32_t), st));
+        rc = ik_solve7(h, sc, joints_dev, system_dev, n, eps, st);
+        if (rc) return rc;
+        k_ik_dls_update<<<(int)((n + 255) / 256), 256, 0, st>>>(sc.tips, target_dev, n, eps, lam, tol, joints_dev, err_dev, iters_dev,
+                                                               sc.frozen, sc.active);
+        h->launches += 1;
+        CTR_CUDA(cudaGetLastError());
+        if ((it & 3) == 3 || it == max_iters - 1) {          // every 4th iteration: has every configuration converged?
+            int32_t active = 0;
+            CTR_CUDA(cudaMemcpyAsync(&active, sc.active, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+            CTR_CUDA(cudaStreamSynchronize(st));
+            if (active == 0) break;
+        }
+    }
+    CTR_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
 

@@ -261,6 +261,31 @@ class CtrReachVecEnv(object):
         t0, t1, t2 = (int(v) for v in tip_idx)
         return r[t1:t0 + 1], r[t2:t1 + 1], r[:t2 + 1]
 
+    def jacobian(self, joints, system=None, eps=1e-4):
+        """Finite-difference position Jacobian (CTR_Python/CTR_Model.py:251-262 over Model.forward_kinematics): joints (n, 6)
+        float64 -> J (n, 3, 6), tip (n, 3)."""
+        q = torch.as_tensor(joints, dtype=torch.float64, device=self.device).reshape(-1, 6).t().contiguous()
+        n = q.shape[1]
+        s = None if system is None else torch.as_tensor(system, dtype=torch.int32, device=self.device).expand(n).contiguous()
+        J = torch.empty((18, n), dtype=torch.float64, device=self.device)
+        tip = torch.empty((3, n), dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.ctr_jacobian(self.handle, _lib.ptr(q), _lib.ptr(s), n, float(eps), _lib.ptr(J), _lib.ptr(tip),
+                                         self._stream()))
+        return J.t().reshape(n, 3, 6), tip.t()
+
+    def ik_dls(self, target, q0, system=None, lam=0.25, eps=1e-4, tol=1e-3, max_iters=500):
+        """Damped-least-squares position IK of the reference's baseline controller (src/jacobian_controller.py:19-73), batched:
+        target (n, 3), q0 (n, 6) -> q (n, 6), err (n,), iters (n,).  Joints are not clipped (the reference does not)."""
+        q = torch.as_tensor(q0, dtype=torch.float64, device=self.device).reshape(-1, 6).t().contiguous().clone()
+        n = q.shape[1]
+        tg = torch.as_tensor(target, dtype=torch.float64, device=self.device).reshape(n, 3).t().contiguous()
+        s = None if system is None else torch.as_tensor(system, dtype=torch.int32, device=self.device).expand(n).contiguous()
+        err = torch.empty(n, dtype=torch.float64, device=self.device)
+        iters = torch.empty(n, dtype=torch.int32, device=self.device)
+        _lib.check(self.lib.ctr_ik_dls(self.handle, _lib.ptr(tg), _lib.ptr(q), _lib.ptr(s), n, float(lam), float(eps), float(tol),
+                                       int(max_iters), _lib.ptr(err), _lib.ptr(iters), self._stream()))
+        return q.t(), err, iters
+
     def set_tube_params(self, params):
         """Per-env derived constants (N, 18) = L, Lc, EI, GJ, Ux, Uy (x3 each) or None (model.py:20-28)."""
         if params is None:

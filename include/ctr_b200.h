@@ -194,6 +194,21 @@ int64_t ctr_launch_count(const ctr_handle *h);
 int ctr_fk_shape(ctr_handle *h, const double *joints_dev, const int32_t *system_dev, const double *params_dev, int64_t n,
                  int32_t max_pts, double *shape_dev, int32_t *npts_dev, int32_t *tip_idx_dev, double *tip_dev, void *stream);
 
+/* ---- finite-difference Jacobian and damped-least-squares inverse kinematics --------------------
+ * The algorithm of the reference's baseline controller (src/jacobian_controller.py:19-73 dls_ik_position_only,
+ * envs/CTR_Python/CTR_Model.py:251-262 jac): forward differences with step eps (reference 1e-4) on the 6 joints, 7 solves
+ * per Jacobian; dq = J^T (J J^T + lam I)^-1 (target - tip), lam 0.25; a configuration stops once the error before its update
+ * was below tol (reference 1e-3 m), at most max_iters (reference 500).  Joints are NOT clipped to the joint box (the reference
+ * does not).  The reference script runs on the out-of-scope BVP model and cannot be executed: here the kinematics are
+ * ctr_fk's, and parity is pinned to oracle/ik_oracle.py only.
+ * ctr_jacobian: joints f64 [6][n] -> J f64 [18][n] (3 x 6 row-major: J[r * 6 + c] = d tip_r / d joint_c), tip f64 [3][n] or NULL.
+ * ctr_ik_dls: target f64 [3][n], joints f64 [6][n] in / out -> err f64 [n] (the last error norm evaluated), iters i32 [n].
+ * Synchronises `stream` (it polls convergence every 4 iterations). */
+int ctr_jacobian(ctr_handle *h, const double *joints_dev, const int32_t *system_dev, int64_t n, double eps, double *J_dev,
+                 double *tip_dev, void *stream);
+int ctr_ik_dls(ctr_handle *h, const double *target_dev, double *joints_dev, const int32_t *system_dev, int64_t n, double lam,
+               double eps, double tol, int32_t max_iters, double *err_dev, int32_t *iters_dev, void *stream);
+
 /* ---- hindsight replay on the device --------------------------------------------------------
  * Replaces what the reference delegates to stable_baselines' HER wrapper (third party, not vendored, version not
  * pinned: setup.py:5; call sites src/utils.py:5-7,27-28; settings saved_policies/.../config.yml: goal_selection_strategy
