@@ -475,6 +475,13 @@ def kernel_table(args, dev, pool, fma_peak, hbm_peak):
                                                     _lib.ptr(tip), st)))
     pts = float(npts.double().sum())
     fma_row("k_fk_shape", sec, fk_flop + pts * 3 * 12.0, "131072 configs; + 12 flop per sample and component; writes %.0f MB" % (pts * 24 / 1e6))
+    # ---- ctr_jacobian: k_ik_perturb + k_fk on 7 x 16384 columns + k_ik_jacobian (the IK loop adds one small update kernel)
+    nj = 16384
+    qj = q[:, :nj].contiguous()
+    Jd = torch.empty((18, nj), dtype=torch.float64, device=dev)
+    sec = timed(lambda: _lib.check(lib.ctr_jacobian(h, _lib.ptr(qj), None, nj, 1e-4, _lib.ptr(Jd), None, st)))
+    fma_row("ctr_jacobian (7 k_fk columns + glue)", sec, 7.0 * fk_flop * nj / N,
+            "16384 configs = 114688 solves; flops taken as 7 x the unperturbed solves' counters")
     # ---- k_reset: CtrReachEnv.reset of every env = 2 FK solves + goal sampling
     def full_reset():
         _lib.check(lib.ctr_reset(h, None, None, None, st))
