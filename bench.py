@@ -648,7 +648,7 @@ def main():
     ap.add_argument('--integrator', default='dp45', choices=['dp45', 'rk4'])
     ap.add_argument('--precision', default='f64', choices=['f64', 'f32'])
     ap.add_argument('--rk4-steps', type=int, default=8)
-    ap.add_argument('--cpu-steps', type=int, default=1500, help='timed steps of the CPU port per process (2 envs each): ~12 s on 16 cores')
+    ap.add_argument('--cpu-steps', type=int, default=2500, help='timed steps of the CPU port per process (2 envs each): ~15 s on 16 cores')
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--no-kernel-table', action='store_true', help='skip the per-kernel roofline table (1 GPU)')
     ap.add_argument('--extras', action='store_true', help='also time the other BASELINE.json configs (1 GPU)')
