@@ -1323,8 +1323,12 @@ static int launch_step_range(ctr_handle* h, KArgs a, const float* action_dev, in
     a.refill_blocks = refill_blocks;
     // U_y == 0 fast path: nominal tubes only (explicit per-env constants may carry any U_y)
     const bool uy0 = h->all_uy_zero && !h->use_params && !getenv("CTR_NO_UY0");
+#ifndef CTR_DEBUG_SKIP_STEP_KERNEL      // measurement-only build: the host pipeline's copies without its kernels
     DISPATCH_STEP(uy0, h->cfg.integrator, h->cfg.precision,
                   <<<grid_for(count) + refill_blocks, BLOCK, 0, st>>>(a, action_dev));
+#else
+    (void)uy0;
+#endif
     h->launches += 1;
     CTR_CUDA(cudaGetLastError());
     return 0;
