@@ -529,11 +529,14 @@ def extras(args, dev, pool):
     from ctr_reach_envs.envs import CtrReachVecEnv
     res = {}
 
-    def time_env(n, steps, **kw):
+    def time_env(n, steps, tol=None, curriculum=None, **kw):
         k = ctr_reach_envs.default_kwargs()
         k.update(kw)
+        if curriculum:            # decay schedule of saved_policies/**/env_parameters.yml (SURVEY 8d cfg 5), advanced every step
+            k['goal_tolerance_parameters'] = dict(k['goal_tolerance_parameters'], **curriculum)
         e = CtrReachVecEnv(n, device=dev.index, **k)
-        e.goal_tolerance.current_tol = args.tol
+        if not curriculum:
+            e.goal_tolerance.current_tol = args.tol if tol is None else tol
         e.reset()
         acts = [p[:n].contiguous() if p.shape[0] >= n else p.repeat((n + p.shape[0] - 1) // p.shape[0], 1)[:n].contiguous() for p in pool[:4]]
         for i in range(5):
@@ -542,6 +545,8 @@ def extras(args, dev, pool):
         s, t = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
         for i in range(steps):
+            if curriculum:
+                e.update_goal_tolerance(1000 * i)           # host-side scalar schedule -> ctr_set_tolerance
             e.step(acts[i % 4])
         t.record()
         torch.cuda.synchronize(dev)
@@ -554,6 +559,12 @@ def extras(args, dev, pool):
         res["%s_%s_131072_envs" % (integ, prec)] = {"value": time_env(ENVS_PER_GPU, 30, integrator=integ, precision=prec), "unit": UNIT,
                                                      "note": "does NOT meet the 1e-5 m bar on all configs (see DESIGN.md)"}
     res["cfg5_domain_rand_131072_envs"] = {"value": time_env(ENVS_PER_GPU, 30, domain_rand=0.05), "unit": UNIT}
+    res["cfg5_domain_rand_tolerance_curriculum_131072_envs"] = {
+        "value": time_env(ENVS_PER_GPU, 30, domain_rand=0.05,
+                          curriculum={'function': 'decay', 'initial_tol': 0.020, 'final_tol': 0.001, 'N_ts': 1.5e6, 'set_tol': 0}),
+        "unit": UNIT, "note": "per-env tube parameters +-5 % at every reset; tolerance 0.02 -> 0.001 decay advanced every step"}
+    res["cfg3_tol_0.001_131072_envs"] = {"value": time_env(ENVS_PER_GPU, 30, tol=0.001), "unit": UNIT,
+                                          "note": "almost nobody succeeds: episodes end at 150 steps, lowest reset load"}
     # cfg 4: HER compute_reward + relabel on 2^20 transitions (HBM bound: 80 B / transition)
     k = ctr_reach_envs.default_kwargs()
     e = CtrReachVecEnv(16, device=dev.index, **k)
