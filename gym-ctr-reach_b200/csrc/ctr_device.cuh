@@ -36,7 +36,32 @@ struct SysConst {
 struct LaneId {
     int lane, g, j;            // lane in warp, group in warp, tube index (lane in group)
     int l0, lnext, lprev;      // absolute lane ids: group lane 0, tube (j+1)%3, tube (j+2)%3
+    int w;                     // warp in block
 };
+
+// ---- lane exchange -------------------------------------------------------------------------------------------
+// CTR_XCH_SMEM = 1 routes the lane exchanges of rhs() and group_sum() through a per-warp shared-memory mailbox
+// (STS / __syncwarp / LDS) instead of __shfl_sync: a 64-bit shuffle is two SHFL.IDX whose halves ptxas then moves into an
+// aligned register pair (112 of the 941 instructions of one Dormand-Prince attempt were such copies).  Same values, same
+// order of operations: results are bit-identical between the two settings.
+#ifndef CTR_BLOCK
+#define CTR_BLOCK 128
+#endif
+#ifndef CTR_XCH_SMEM
+#define CTR_XCH_SMEM 1
+#endif
+#if CTR_XCH_SMEM
+constexpr int XCH_ROWS = 7;    // angle | cos, sin | ux, uy, uz | group_sum partial
+__shared__ double s_xch[CTR_BLOCK / 32][XCH_ROWS][32];
+template <typename T>
+__device__ __forceinline__ void xch_put(const LaneId& id, int row, T v) {
+    reinterpret_cast<T*>(&s_xch[id.w][row][0])[id.lane] = v;
+}
+template <typename T>
+__device__ __forceinline__ T xch_get(const LaneId& id, int row, int lane) {
+    return reinterpret_cast<const T*>(&s_xch[id.w][row][0])[lane];
+}
+#endif
 
 __device__ __forceinline__ LaneId lane_id() {
     LaneId id;
@@ -44,8 +69,9 @@ __device__ __forceinline__ LaneId lane_id() {
     id.g = id.lane / GROUP;
     id.j = id.lane - id.g * GROUP;
     id.l0 = id.g * GROUP;
-    id.lnext = id.l0 + (id.j + 1) % GROUP;
-    id.lprev = id.l0 + (id.j + 2) % GROUP;
+    id.lnext = (id.l0 + (id.j + 1) % GROUP) & 31;   // & 31: the idle lanes 30 / 31 wrap like a shuffle source lane does
+    id.lprev = (id.l0 + (id.j + 2) % GROUP) & 31;
+    id.w = threadIdx.x >> 5;
     return id;
 }
 
@@ -57,9 +83,16 @@ __device__ __forceinline__ T pick3(int j, T a0, T a1, T a2) {
 // (p0 + p1) + p2 of the three lanes' partials, identical bits on all three lanes.
 template <typename T>
 __device__ __forceinline__ T group_sum(const LaneId& id, T p) {
+#if CTR_XCH_SMEM
+    __syncwarp();              // the previous round's readers of row 6 are done
+    xch_put(id, 6, p);
+    __syncwarp();
+    const T p0 = xch_get<T>(id, 6, id.l0), p1 = xch_get<T>(id, 6, id.l0 + 1), p2 = xch_get<T>(id, 6, (id.l0 + 2) & 31);
+#else
     T p0 = __shfl_sync(FULL, p, id.l0);
     T p1 = __shfl_sync(FULL, p, id.l0 + 1);
     T p2 = __shfl_sync(FULL, p, id.l0 + 2);
+#endif
     return (p0 + p1) + p2;
 }
 
@@ -355,12 +388,30 @@ __device__ __forceinline__ bool needs_slow_trig(int j, const double* alpha) {
 template <typename T, bool SLOW, bool UY0>
 __device__ __forceinline__ void rhs(const LaneId& id, const Section<T>& sc, bool do_trig, Trig<T>& tg, const T (&Y)[6],
                                     T (&D)[6]) {
+#if CTR_XCH_SMEM
+    // Mailbox rows 0 | 1, 2 | 3, 4, 5 are written in that order with a warp barrier after each group, so a row is
+    // rewritten (by the next call) only after two further barriers -- or the explicit one below when the trig phases are skipped.
+    if (do_trig) {   // warp-uniform
+        xch_put(id, 0, Y[1]);
+        __syncwarp();
+        const T a_next = xch_get<T>(id, 0, id.lnext);
+        sincos_t<SLOW>(Y[1] - a_next, &tg.so, &tg.co);
+        xch_put(id, 1, tg.co);
+        xch_put(id, 2, tg.so);
+        __syncwarp();
+        tg.cp = xch_get<T>(id, 1, id.lprev);
+        tg.sp = xch_get<T>(id, 2, id.lprev);
+    } else {
+        __syncwarp();
+    }
+#else
     if (do_trig) {   // warp-uniform
         const T a_next = __shfl_sync(FULL, Y[1], id.lnext);
         sincos_t<SLOW>(Y[1] - a_next, &tg.so, &tg.co);
         tg.cp = __shfl_sync(FULL, tg.co, id.lprev);
         tg.sp = __shfl_sync(FULL, tg.so, id.lprev);
     }
+#endif
     // model.py:87-94 with cos(0) = 1, sin(0) = 0 folded; sin(alpha_j - alpha_{j-1}) = -sp
     T ux, uy;
     if (UY0) {
@@ -381,9 +432,17 @@ __device__ __forceinline__ void rhs(const LaneId& id, const Section<T>& sc, bool
         D[0] = fma_t(ux, sc.ky, -(uy * sc.kx));              // model.py:101  (0 when absent: kx = ky = 0)
     }
     D[1] = sc.present * Y[0];                            // model.py:99,102
+#if CTR_XCH_SMEM
+    xch_put(id, 3, ux);
+    xch_put(id, 4, uy);
+    xch_put(id, 5, Y[0]);
+    __syncwarp();
+    const T ux0 = xch_get<T>(id, 3, id.l0), uy0 = xch_get<T>(id, 4, id.l0), uz0 = xch_get<T>(id, 5, id.l0);
+#else
     const T ux0 = __shfl_sync(FULL, ux, id.l0);
     const T uy0 = __shfl_sync(FULL, uy, id.l0);
     const T uz0 = __shfl_sync(FULL, Y[0], id.l0);
+#endif
     D[2] = Y[5];                                         // r' = R e3          (model.py:108)
     D[3] = fma_t(Y[4], uz0, -(Y[5] * uy0));              // R' = R u_hat, row j (model.py:107,109)
     D[4] = fma_t(Y[5], ux0, -(Y[3] * uz0));
