@@ -51,15 +51,29 @@ struct LaneId {
 #define CTR_XCH_SMEM 1
 #endif
 #if CTR_XCH_SMEM
-constexpr int XCH_ROWS = 7;    // angle | cos, sin | ux, uy, uz | group_sum partial
-__shared__ double s_xch[CTR_BLOCK / 32][XCH_ROWS][32];
+// Mailbox: three rows of value PAIRS (one STS.128 / LDS.128 each in float64) and one row of single values per warp.
 template <typename T>
-__device__ __forceinline__ void xch_put(const LaneId& id, int row, T v) {
-    reinterpret_cast<T*>(&s_xch[id.w][row][0])[id.lane] = v;
+struct alignas(2 * sizeof(T)) XPair {
+    T a, b;
+};
+// rows: (uz, angle) | (cos, sin) | (ux, uy) | (group_sum partial, -).  All four share one base register per lane, the row is an
+// immediate offset; 34 entries per row so that l0 + 2 of the idle lanes 30 / 31 stays inside the row's storage.
+__shared__ XPair<double> s_xp[CTR_BLOCK / 32][4][34];
+template <typename T>
+__device__ __forceinline__ void xch_put2(const LaneId& id, int row, T a, T b) {
+    reinterpret_cast<XPair<T>*>(&s_xp[id.w][row][0])[id.lane] = XPair<T>{a, b};
 }
 template <typename T>
-__device__ __forceinline__ T xch_get(const LaneId& id, int row, int lane) {
-    return reinterpret_cast<const T*>(&s_xch[id.w][row][0])[lane];
+__device__ __forceinline__ XPair<T> xch_get2(const LaneId& id, int row, int lane) {
+    return reinterpret_cast<const XPair<T>*>(&s_xp[id.w][row][0])[lane];
+}
+template <typename T>
+__device__ __forceinline__ T xch_get2a(const LaneId& id, int row, int lane) {
+    return reinterpret_cast<const XPair<T>*>(&s_xp[id.w][row][0])[lane].a;
+}
+template <typename T>
+__device__ __forceinline__ T xch_get2b(const LaneId& id, int row, int lane) {
+    return reinterpret_cast<const XPair<T>*>(&s_xp[id.w][row][0])[lane].b;
 }
 #endif
 
@@ -84,10 +98,11 @@ __device__ __forceinline__ T pick3(int j, T a0, T a1, T a2) {
 template <typename T>
 __device__ __forceinline__ T group_sum(const LaneId& id, T p) {
 #if CTR_XCH_SMEM
-    __syncwarp();              // the previous round's readers of row 6 are done
-    xch_put(id, 6, p);
+    __syncwarp();              // the previous round's readers of the row are done
+    reinterpret_cast<XPair<T>*>(&s_xp[id.w][3][0])[id.lane].a = p;
     __syncwarp();
-    const T p0 = xch_get<T>(id, 6, id.l0), p1 = xch_get<T>(id, 6, id.l0 + 1), p2 = xch_get<T>(id, 6, (id.l0 + 2) & 31);
+    const XPair<T>* row = reinterpret_cast<const XPair<T>*>(&s_xp[id.w][3][0]) + id.l0;
+    const T p0 = row[0].a, p1 = row[1].a, p2 = row[2].a;
 #else
     T p0 = __shfl_sync(FULL, p, id.l0);
     T p1 = __shfl_sync(FULL, p, id.l0 + 1);
@@ -103,6 +118,13 @@ __device__ __forceinline__ double abs_t(double a) { return fabs(a); }
 __device__ __forceinline__ float abs_t(float a) { return fabsf(a); }
 __device__ __forceinline__ double max_t(double a, double b) { return fmax(a, b); }
 __device__ __forceinline__ float max_t(float a, float b) { return fmaxf(a, b); }
+// min / max by compare-and-select: equal to fmin / fmax whenever neither operand is NaN (the sign of a zero aside), 3 instructions
+// instead of the 6 of the NaN-quieting library form (sm_100 has no FP64 min / max instruction).  A NaN operand may come out as NaN:
+// every caller sits on a path where a NaN already marks the solve as failed (rk.py:129-130 analogue in fk_dp45).
+__device__ __forceinline__ double dmin(double a, double b) { return a < b ? a : b; }
+__device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
+__device__ __forceinline__ double maxabs_t(double a, double b) { return dmax(fabs(a), fabs(b)); }
+__device__ __forceinline__ float maxabs_t(float a, float b) { return fmaxf(fabsf(a), fabsf(b)); }
 
 // 1/x for normal positive x: MUFU.RCP64H seed + two Newton steps (relative error < 2^-52; no special cases, no
 // slow-path call -- the compiler's '/' costs ~3x as much and a branch).
@@ -284,7 +306,7 @@ struct GroupScratch {            // 312 B: 78 words, so the 10 groups of a warp 
 };
 
 __device__ __forceinline__ void cswap(double& a, double& b) {
-    double lo = fmin(a, b), hi = fmax(a, b);
+    const double lo = dmin(a, b), hi = dmax(b, a);   // one of each for every pair of values, NaN or not
     a = lo;
     b = hi;
 }
@@ -303,7 +325,7 @@ __device__ __forceinline__ void build_sections(const double* L, const double* Lc
         p[4 + i] = dc[i];
         p[7 + i] = dtip[i];
     }
-    const double bmin = fmin(fmin(beta[0], beta[1]), beta[2]);   // Segment.py:53 min(base)
+    const double bmin = dmin(dmin(beta[0], beta[1]), beta[2]);   // Segment.py:53 min(base)
     // 29-comparator sorting network for 10 keys (Segment.py:15-16 np.sort; tie order is irrelevant)
 #define CS(a, b) cswap(p[a], p[b])
     CS(0, 8); CS(1, 9); CS(2, 7); CS(3, 5); CS(4, 6);
@@ -389,20 +411,18 @@ template <typename T, bool SLOW, bool UY0>
 __device__ __forceinline__ void rhs(const LaneId& id, const Section<T>& sc, bool do_trig, Trig<T>& tg, const T (&Y)[6],
                                     T (&D)[6]) {
 #if CTR_XCH_SMEM
-    // Mailbox rows 0 | 1, 2 | 3, 4, 5 are written in that order with a warp barrier after each group, so a row is
-    // rewritten (by the next call) only after two further barriers -- or the explicit one below when the trig phases are skipped.
+    // Pair rows 0 | 1 | 2 are written in that order with a warp barrier after each, and every read of a row sits before the
+    // barrier that precedes the row's next write (uz_0 of row 0 is therefore fetched before the last barrier of the call).
+    xch_put2(id, 0, Y[0], Y[1]);
+    __syncwarp();
     if (do_trig) {   // warp-uniform
-        xch_put(id, 0, Y[1]);
-        __syncwarp();
-        const T a_next = xch_get<T>(id, 0, id.lnext);
+        const T a_next = xch_get2b<T>(id, 0, id.lnext);
         sincos_t<SLOW>(Y[1] - a_next, &tg.so, &tg.co);
-        xch_put(id, 1, tg.co);
-        xch_put(id, 2, tg.so);
+        xch_put2(id, 1, tg.co, tg.so);
         __syncwarp();
-        tg.cp = xch_get<T>(id, 1, id.lprev);
-        tg.sp = xch_get<T>(id, 2, id.lprev);
-    } else {
-        __syncwarp();
+        const XPair<T> pr = xch_get2<T>(id, 1, id.lprev);
+        tg.cp = pr.a;
+        tg.sp = pr.b;
     }
 #else
     if (do_trig) {   // warp-uniform
@@ -433,11 +453,11 @@ __device__ __forceinline__ void rhs(const LaneId& id, const Section<T>& sc, bool
     }
     D[1] = sc.present * Y[0];                            // model.py:99,102
 #if CTR_XCH_SMEM
-    xch_put(id, 3, ux);
-    xch_put(id, 4, uy);
-    xch_put(id, 5, Y[0]);
+    const T uz0 = xch_get2a<T>(id, 0, id.l0);
+    xch_put2(id, 2, ux, uy);
     __syncwarp();
-    const T ux0 = xch_get<T>(id, 3, id.l0), uy0 = xch_get<T>(id, 4, id.l0), uz0 = xch_get<T>(id, 5, id.l0);
+    const XPair<T> u0 = xch_get2<T>(id, 2, id.l0);
+    const T ux0 = u0.a, uy0 = u0.b;
 #else
     const T ux0 = __shfl_sync(FULL, ux, id.l0);
     const T uy0 = __shfl_sync(FULL, uy, id.l0);
@@ -581,7 +601,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
             const double m1 = (double)group_sum(id, p1) * (1.0 / 18.0);   // d1^2
             const double interval = fabs(tf - t);
             double h0 = (m0 < 1e-10 || m1 < 1e-10) ? 1e-6 : 0.01 * sqrt_fast(m0 * rcp_fast(m1));
-            h0 = fmin(h0, interval);
+            h0 = dmin(h0, interval);
             const T h0t = (T)h0;
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(h0t, f[i], y[i]);   // common.py:113
@@ -594,11 +614,11 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
                 p2 = fma_t(c, c, p2);
             }
             const double m2 = (double)group_sum(id, p2) * (1.0 / 18.0) * rcp_fast(h0 * h0);   // d2^2
-            const double M = fmax(m1, m2);
+            const double M = dmax(m1, m2);
             // h1 = (0.01 / max(d1, d2))^(1/5) = (1e4 M)^(-1/10)
-            const double h1 = (M <= 1e-30) ? fmax(1e-6, h0 * 1e-3) : pow_m01(fmin(fmax(M * 1e4, 1e-30), 1e30));
+            const double h1 = (M <= 1e-30) ? dmax(1e-6, h0 * 1e-3) : pow_m01(dmin(dmax(M * 1e4, 1e-30), 1e30));
             if (init) {
-                h_abs = fmin(fmin(100.0 * h0, h1), interval);
+                h_abs = dmin(dmin(100.0 * h0, h1), interval);
                 info.nfev += 2;
             }
         }
@@ -661,19 +681,19 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
 #pragma unroll
         for (int i = 0; i < 6; ++i) {
             const T e = fma_t(dpc<T>(E7), k7[i], e5[i]);
-            const T sc_i = fma_t(max_t(abs_t(y[i]), abs_t(Y[i])), rtol, atol);      // rk.py:141
+            const T sc_i = fma_t(maxabs_t(y[i], Y[i]), rtol, atol);                  // rk.py:141
             const T q = e * rcp_t(sc_i);
             pe = fma_t(q, q, pe);
         }
         const double m = (double)group_sum(id, pe) * (h_d * h_d) * (1.0 / 18.0);    // error_norm^2 (rk.py:142)
         const bool accept = m < 1.0;                                                // rk.py:144
-        const double fac = 0.9 * pow_m01(fmin(fmax(m, 1e-14), 1e10));               // SAFETY * norm^(-1/5)
+        const double fac = 0.9 * pow_m01(dmin(dmax(m, 1e-14), 1e10));               // SAFETY * norm^(-1/5)
         double factor;
         if (accept) {
-            factor = (m == 0.0) ? 10.0 : fmin(10.0, fac);                           // rk.py:145-149
-            if (rejected) factor = fmin(1.0, factor);                               // rk.py:151-152
+            factor = (m == 0.0) ? 10.0 : dmin(fac, 10.0);                           // rk.py:145-149
+            if (rejected) factor = dmin(factor, 1.0);                               // rk.py:151-152
         } else {
-            factor = fmax(0.2, fac);                                                // rk.py:157-158
+            factor = dmax(fac, 0.2);                                                // rk.py:157-158
         }
         if (active) {
             attempts += 1;

@@ -54,6 +54,9 @@ constexpr int ENVS_PER_BLOCK = (BLOCK / 32) * ENVS_PER_WARP;
 #ifndef CTR_SORT_WINDOW
 #define CTR_SORT_WINDOW 640
 #endif
+#ifndef CTR_SORT_DESC
+#define CTR_SORT_DESC 1
+#endif
 constexpr int SORT_WINDOW = CTR_SORT_WINDOW;                 // slots per sorting window (16 blocks); launches start on window boundaries
 constexpr int N_STATS = 16;
 enum { ST_EPISODES = 0, ST_SUCCESSES, ST_SUM_ERROR, ST_SUM_RETURN, ST_SUM_LENGTH, ST_STEPS, ST_RESETS, ST_DRAWS,
@@ -501,7 +504,12 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_step(const KArgs a, const
 #pragma unroll
                 for (int k = 0; k < PER; ++k) {
                     const int i = threadIdx.x + k * BLOCK;
+#if CTR_SORT_DESC
+                    // heaviest environments first: the blocks dispatched last in a window (and in the launch) are its lightest
+                    if (bin[k] >= 0) a.perm[gbase + (nslots - 1 - (s_hist[bin[k]] + rank[k]))] = (int32_t)(gbase + i);
+#else
                     if (bin[k] >= 0) a.perm[gbase + s_hist[bin[k]] + rank[k]] = (int32_t)(gbase + i);
+#endif
                 }
             }
         }

@@ -15,7 +15,7 @@ import numpy as np
 import ctr_oracle as O
 import ctr_oracle_c as C
 
-A_COST, I_COST = 450.0, 150.0
+A_COST, I_COST = 867.0, 435.0   # warp instructions per attempt pass / per initial-step block (profiles/r1s ncu source page)
 
 
 def attempts(tc, q, nthreads=8):
