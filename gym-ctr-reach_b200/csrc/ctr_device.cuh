@@ -4,11 +4,12 @@
 //   y_j = { uz_j, alpha_j, r_j, R[j][0], R[j][1], R[j][2] }
 // i.e. the torsion pair of tube j, component j of the position and ROW j of the rotation matrix.  The 18-dim ODE
 // of the reference (model.py:72-117) couples these slices only through
-//   * the three angle differences  (one sincos per lane, the other one arrives by shuffle), and
+//   * the three angle differences  (one sincos per lane, the other one arrives from the neighbouring lane), and
 //   * (ux_0, uy_0, uz_0) of tube 0  (broadcast from lane 0 of the group).
 // so the whole Dormand-Prince state (y, 7 stage derivatives) is 6 x 8 values per lane and stays in registers
-// even in float64.  A warp carries 10 environments (lanes 30/31 idle).  All shuffles are executed at
-// warp-uniform program points with the full mask; per-environment control flow is expressed by predication.
+// even in float64.  A warp carries 10 environments (lanes 30/31 idle).  The lane exchanges go through a per-warp
+// shared-memory mailbox (CTR_XCH_SMEM, below) at warp-uniform program points; per-environment control flow is
+// expressed by predication.
 //
 // Reference citations are relative to /root/reference/ctr_reach_envs/ ; "rk.py"/"common.py" are
 // scipy/integrate/_ivp/* (the third-party integrator the reference calls, model.py:149-151).
