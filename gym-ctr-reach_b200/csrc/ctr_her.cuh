@@ -42,6 +42,10 @@ __global__ void k_her_begin(const ctr_her_ring r, const HerSrc s) {
 
 constexpr int HER_REC = CTR_HER_RECORD;      // doubles per record (352 B = 11 sectors)
 constexpr int HER_PAD = HER_REC + 1;         // shared-memory row stride (odd: the row-wise reads of phase 3 spread over banks)
+#ifndef CTR_HER_MLP
+#define CTR_HER_MLP 4
+#endif
+constexpr int HER_MLP = CTR_HER_MLP;         // records a warp loads per batch in k_her_sample (power of two <= 32)
 constexpr int HER_WARPS = 2;                 // warps per sampling block: 2 x 32 x 45 x 8 B = 23 KB of shared memory
 
 // One warp per 32 environments.  Phase 1 (lane = env): the env's SoA rows are read coalesced, the record is assembled in
@@ -142,12 +146,25 @@ __global__ void __launch_bounds__(32 * HER_WARPS) k_her_sample(const ctr_her_rin
         }
     }
     // ---- phase 2
-    for (int smp = 0; smp < 32; ++smp) {
-        const int64_t c = __shfl_sync(FULL, col, smp), g = __shfl_sync(FULL, gcol, smp);
-        const double* rec = r.rec + c * HER_REC;
-        s_rec[w][smp][lane] = rec[lane];
-        if (lane < HER_REC - 32) s_rec[w][smp][32 + lane] = rec[32 + lane];
-        if (g >= 0 && lane < 3) s_goal[w][smp][lane] = r.rec[g * HER_REC + 2 * D + 3 + lane];
+    // HER_MLP records per batch: all their loads are issued before the first shared-memory store, so a warp keeps
+    // HER_MLP x 376 bytes in flight instead of one record (the kernel is latency bound: random 352-byte reads)
+#pragma unroll 1
+    for (int s0 = 0; s0 < 32; s0 += HER_MLP) {
+        double v0[HER_MLP], v1[HER_MLP], vg[HER_MLP];
+#pragma unroll
+        for (int u = 0; u < HER_MLP; ++u) {
+            const int64_t c = __shfl_sync(FULL, col, s0 + u), g = __shfl_sync(FULL, gcol, s0 + u);
+            const double* rec = r.rec + c * HER_REC;
+            v0[u] = __ldg(rec + lane);
+            v1[u] = (lane < HER_REC - 32) ? __ldg(rec + 32 + lane) : 0.0;
+            vg[u] = (g >= 0 && lane < 3) ? __ldg(r.rec + g * HER_REC + 2 * D + 3 + lane) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < HER_MLP; ++u) {
+            s_rec[w][s0 + u][lane] = v0[u];
+            if (lane < HER_REC - 32) s_rec[w][s0 + u][32 + lane] = v1[u];
+            if (lane < 3) s_goal[w][s0 + u][lane] = vg[u];
+        }
     }
     __syncwarp();
     // ---- phase 3 (lane = sample)
