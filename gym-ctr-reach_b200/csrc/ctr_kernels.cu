@@ -9,6 +9,7 @@
 //   k_set_action           standalone constraint op        (Obs.set_action, obs.py:166-183)
 //   k_mask_to_list         compaction of an explicit reset mask
 #include <cuda_runtime.h>
+#include <chrono>
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -1507,6 +1508,10 @@ static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_h
         g = &h->graphs.back();
     }
     g->stamp = ++h->graph_clock;
+#ifdef CTR_HOST_TIMING
+    static double t_set = 0, t_launch = 0, t_sync = 0; static int t_n = 0;
+    auto T0 = std::chrono::steady_clock::now();
+#endif
     // refresh the per-step kernel arguments (goal tolerance, refill-queue roles, seed) of every chunk's k_step node
     const float* act_dev = h->stage_action;
     for (size_t i = 0; i < g->knodes.size(); ++i) {
@@ -1520,10 +1525,23 @@ static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_h
         kp.extra = nullptr;
         CTR_CUDA(cudaGraphExecKernelNodeSetParams(g->exec, g->knodes[i], &kp));
     }
+#ifdef CTR_HOST_TIMING
+    auto T1 = std::chrono::steady_clock::now();
+#endif
     CTR_CUDA(cudaGraphLaunch(g->exec, s0));
+#ifdef CTR_HOST_TIMING
+    auto T2 = std::chrono::steady_clock::now();
+#endif
     h->launches += (int64_t)g->knodes.size();
     h->step_index += 1;
     CTR_CUDA(cudaStreamSynchronize(s0));
+#ifdef CTR_HOST_TIMING
+    auto T3 = std::chrono::steady_clock::now();
+    t_set += std::chrono::duration<double, std::micro>(T1 - T0).count();
+    t_launch += std::chrono::duration<double, std::micro>(T2 - T1).count();
+    t_sync += std::chrono::duration<double, std::micro>(T3 - T2).count();
+    if (++t_n % 20 == 0) { fprintf(stderr, "[host step] set-params %.1f us, graph launch %.1f us, sync wait %.1f us (mean of 20)\n", t_set / 20, t_launch / 20, t_sync / 20); t_set = t_launch = t_sync = 0; }
+#endif
     return 0;
 }
 
