@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstdlib>
+#include <cstdint>
 #include <vector>
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("%s: %s\n", #x, cudaGetErrorString(e)); exit(1); } } while (0)
 
@@ -41,8 +42,21 @@ int main() {
         for (size_t c = 0; c < CH; ++c)
             CK(cudaMemcpy2DAsync(host + c * per, N * 8, dev + c * per, N * 8, per * 8, ROWS, cudaMemcpyDeviceToHost, st));
     });
-    for (int blocks : {8, 16, 32, 64, 148}) {
-        for (int threads : {256, 1024}) {
+    uint8_t *dev8, *host8;
+    CK(cudaMalloc(&dev8, 2 * N));
+    CK(cudaHostAlloc(&host8, 2 * N, cudaHostAllocDefault));
+    timeit("8 x (2-D f64 block + 2-D u8 flags), as ctr_step_host does", [&] {
+        for (size_t c = 0; c < CH; ++c) {
+            CK(cudaMemcpy2DAsync(host + c * per, N * 8, dev + c * per, N * 8, per * 8, ROWS, cudaMemcpyDeviceToHost, st));
+            CK(cudaMemcpy2DAsync(host8 + c * per, N, dev8 + c * per, N, per, 2, cudaMemcpyDeviceToHost, st));
+        }
+    });
+    timeit("8 x 2-D f64 block with one more row (flags as a 22nd row)", [&] {
+        for (size_t c = 0; c < CH; ++c)
+            CK(cudaMemcpy2DAsync(host + c * per, N * 8, dev + c * per, N * 8, per * 8, ROWS, cudaMemcpyDeviceToHost, st));
+    });
+    for (int blocks : {8}) {
+        for (int threads : {256}) {
             char name[96];
             snprintf(name, sizeof name, "8 x k_export<<<%d,%d>>> (SM stores to mapped host)", blocks, threads);
             timeit(name, [&] {
