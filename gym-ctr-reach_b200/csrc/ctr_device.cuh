@@ -714,10 +714,11 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
                         q = __dadd_rn(q, __dmul_rn((double)k6[2], c_dpP[20 + pw]));
                         Q[pw] = __dadd_rn(q, __dmul_rn((double)k7[2], c_dpP[24 + pw]));
                     }
+                    const double inv_h = __ddiv_rn(1.0, h_d);   // one division per accepted step; x differs from numpy's (te - t) / h by <= 1 ulp
                     while (sh_i < SHAPE_SAMPLES) {
                         const double te = shape_abscissa(sh_i, sh_a, sh_step, tf);
                         if (!(te <= t_new)) break;                                  // ivp.py: searchsorted(t_eval, t, 'right')
-                        const double x = __ddiv_rn(__dsub_rn(te, t), h_d);
+                        const double x = __dmul_rn(__dsub_rn(te, t), inv_h);
                         const double x2 = __dmul_rn(x, x), x3 = __dmul_rn(x2, x), x4 = __dmul_rn(x3, x);   // np.cumprod
                         double acc = __dmul_rn(Q[0], x);
                         acc = __dadd_rn(acc, __dmul_rn(Q[1], x2));
@@ -849,13 +850,14 @@ __device__ __forceinline__ void fk_group(const LaneId& id, bool valid, GroupScra
 }
 
 // FK with backbone samples (float64 parity integrator only): same section table and integrator as fk_group.
+template <bool UY0>
 __device__ __forceinline__ void fk_group_shape(const LaneId& id, bool valid, GroupScratch& gs, const double* L,
                                                const double* Lc, const double* der, const double* beta, const double* alpha,
                                                double rtol_d, double atol_d, double (&y)[6], FkInfo& info,
                                                const ShapeOut shape) {
     build_sections(L, Lc, beta, gs, id.j == 0);
-    if (needs_slow_trig(id.j, alpha)) fk_dp45<double, true, false, true>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info, shape);
-    else fk_dp45<double, false, false, true>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info, shape);
+    if (needs_slow_trig(id.j, alpha)) fk_dp45<double, true, UY0, true>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info, shape);
+    else fk_dp45<double, false, UY0, true>(id, valid, gs, der, alpha, rtol_d, atol_d, y, info, shape);
     __syncwarp();
 }
 

@@ -243,6 +243,8 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk(const SysConst* __rest
 // Backbone shape: Model.r and tip_pos of the reference (model.py:66-68,137-172) -- 30 samples per
 // section from the integrator's dense output, and for every tube the first sample index whose abscissa reaches
 // L_k + beta_k - 1e-3 (the split points of r1 / r2 / r3).  shape f64 [n][max_pts][3], npts i32 [n], tip_idx i32 [3][n].
+// UY0: every system has y_curvature == 0 and no per-env parameters are given (the instantiation k_step uses, see rhs()).
+template <bool UY0>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk_shape(const SysConst* __restrict__ sys, int n_systems,
                                                     const double* __restrict__ joints, const int32_t* __restrict__ system,
                                                     const double* __restrict__ params, int64_t n, double rtol, double atol,
@@ -274,7 +276,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk_shape(const SysConst* 
     so.base = shape + (e * max_pts) * 3 + id.j;      // [n][max_pts][3]: an env's polyline is contiguous, its 3 lanes write 24 B
     so.stride = 3;
     so.max_pts = valid ? max_pts : 0;
-    fk_group_shape(id, valid, gs, LL, LL + 3, der, beta, alpha, rtol, atol, y, info, so);
+    fk_group_shape<UY0>(id, valid, gs, LL, LL + 3, der, beta, alpha, rtol, atol, y, info, so);
     if (valid) {
         // tip_pos[j] = np.argmax(Length >= d_tip[j] - 1e-3) over the concatenated abscissae (0 when none qualifies)
         const double thr = __dsub_rn(__dadd_rn(pick3(id.j, LL[0], LL[1], LL[2]), pick3(id.j, beta[0], beta[1], beta[2])), 1e-3);
@@ -1718,9 +1720,14 @@ int ctr_fk_shape(ctr_handle* h, const double* joints_dev, const int32_t* system_
     if (max_pts < 1) CTR_FAIL("max_pts must be >= 1");
     if (n <= 0) return 0;
     CTR_CUDA(cudaSetDevice(h->device));
-    k_fk_shape<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(h->sys_dev, h->cfg.n_systems, joints_dev, system_dev, params_dev,
-                                                               n, h->cfg.rtol, h->cfg.atol, max_pts, shape_dev, npts_dev,
-                                                               tip_idx_dev, tip_dev, h->p.stats);
+    if (h->all_uy_zero && !params_dev && !getenv("CTR_NO_UY0"))
+        k_fk_shape<true><<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(h->sys_dev, h->cfg.n_systems, joints_dev, system_dev, params_dev, n,
+                                                                         h->cfg.rtol, h->cfg.atol, max_pts, shape_dev, npts_dev,
+                                                                         tip_idx_dev, tip_dev, h->p.stats);
+    else
+        k_fk_shape<false><<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(h->sys_dev, h->cfg.n_systems, joints_dev, system_dev, params_dev, n,
+                                                                          h->cfg.rtol, h->cfg.atol, max_pts, shape_dev, npts_dev,
+                                                                          tip_idx_dev, tip_dev, h->p.stats);
     h->launches += 1;
     CTR_CUDA(cudaGetLastError());
     return 0;
