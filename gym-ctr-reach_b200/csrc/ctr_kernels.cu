@@ -857,6 +857,7 @@ struct ctr_handle {
     std::vector<void*> allocs;
     cudaStream_t stream;       // used by the *_host entry points (= streams[0])
     cudaStream_t streams[N_COMPUTE_STREAMS + 1];   // ctr_step_host: compute streams (chunks round-robin) + one copy-back stream
+    int host_flags_late;       // ctr_step_host: done / success bytes in one copy after the last chunk ($CTR_HOST_FLAGS_LATE, default 1)
     int host_chunks;           // chunks per ctr_step_host call (0: one per 16384 envs, at most 16); $CTR_HOST_CHUNKS
     int host_graphs;           // replay the pipeline as a CUDA graph (default; $CTR_HOST_GRAPH=0 submits call by call)
     cudaEvent_t ev_fork, ev_join[N_COMPUTE_STREAMS + 1], ev_chunk[16];
@@ -1132,6 +1133,7 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     for (int k = 0; k < 16; ++k) CTR_CUDA(cudaEventCreateWithFlags(&h->ev_chunk[k], cudaEventDisableTiming));
     h->host_chunks = getenv("CTR_HOST_CHUNKS") ? atoi(getenv("CTR_HOST_CHUNKS")) : 0;
     h->host_graphs = getenv("CTR_HOST_GRAPH") ? atoi(getenv("CTR_HOST_GRAPH")) : 1;
+    h->host_flags_late = getenv("CTR_HOST_FLAGS_LATE") ? atoi(getenv("CTR_HOST_FLAGS_LATE")) : 1;
     h->graph_clock = 0;
     CTR_CUDA(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
     void* f[CTR_F_COUNT] = {h->p.joints, h->p.desired_goal, h->p.desired_joints, h->p.starting_joints,
@@ -1407,11 +1409,23 @@ static int enqueue_host_step(ctr_handle* h, const KArgs& a, int64_t per, const f
             if (reward_host) CTR_CUDA(cudaMemcpyAsync(reward_host + b, h->p.reward + b, w, cudaMemcpyDeviceToHost, st));
             if (error_host) CTR_CUDA(cudaMemcpyAsync(error_host + b, h->p.error + b, w, cudaMemcpyDeviceToHost, st));
         }
+        if (!h->host_flags_late) {
+            if (packed) {
+                CTR_CUDA(cudaMemcpy2DAsync(done_host + b, (size_t)N, h->p.done + b, (size_t)N, (size_t)cnt, 2, cudaMemcpyDeviceToHost, st));
+            } else {
+                if (done_host) CTR_CUDA(cudaMemcpyAsync(done_host + b, h->p.done + b, cnt, cudaMemcpyDeviceToHost, st));
+                if (success_host) CTR_CUDA(cudaMemcpyAsync(success_host + b, h->p.success + b, cnt, cudaMemcpyDeviceToHost, st));
+            }
+        }
+    }
+    if (h->host_flags_late) {
+        // the done / success bytes of ALL chunks in one copy behind the last chunk's results (the copy stream has waited for
+        // every chunk's kernel by now): a 16 KB copy per chunk costs ~4 us of the copy stream, as much as 200 KB of results
         if (packed) {
-            CTR_CUDA(cudaMemcpy2DAsync(done_host + b, (size_t)N, h->p.done + b, (size_t)N, (size_t)cnt, 2, cudaMemcpyDeviceToHost, st));
+            CTR_CUDA(cudaMemcpyAsync(done_host, h->p.done, (size_t)(2 * N), cudaMemcpyDeviceToHost, sc));
         } else {
-            if (done_host) CTR_CUDA(cudaMemcpyAsync(done_host + b, h->p.done + b, cnt, cudaMemcpyDeviceToHost, st));
-            if (success_host) CTR_CUDA(cudaMemcpyAsync(success_host + b, h->p.success + b, cnt, cudaMemcpyDeviceToHost, st));
+            if (done_host) CTR_CUDA(cudaMemcpyAsync(done_host, h->p.done, (size_t)N, cudaMemcpyDeviceToHost, sc));
+            if (success_host) CTR_CUDA(cudaMemcpyAsync(success_host, h->p.success, (size_t)N, cudaMemcpyDeviceToHost, sc));
         }
     }
     for (int k = 1; k <= N_COMPUTE_STREAMS; ++k) {
