@@ -565,7 +565,7 @@ def test_single_env_facade_matches_oracle_episode(oracle_py):
             env.close()
 
 
-def test_host_step_entry_point_matches_device_path(vec_factory):
+def test_host_step_entry_point_matches_device_path(vec_factory, monkeypatch):
     from ctr_reach_envs import _lib
     n = 2048
     envs = [vec_factory(n, seed=3), vec_factory(n, seed=3)]
@@ -589,25 +589,29 @@ def test_host_step_entry_point_matches_device_path(vec_factory):
         assert np.array_equal(h_ach.T, obs['achieved_goal'].cpu().numpy())
         assert np.array_equal(h_rew, reward.cpu().numpy()) and np.array_equal(h_done, done.cpu().numpy())
         assert np.array_equal(h_err, info['error'].cpu().numpy())
+        assert np.array_equal(h_succ, info['is_success'].cpu().numpy().astype(np.uint8))
     # packed variant (two host blocks in the device's row order) and the chunked pipeline: 70 000 envs = 5 chunks
+    # (flag bytes in one copy behind the last chunk -- the default -- and one copy per chunk)
     n = 70000
-    envs = [vec_factory(n, seed=4), vec_factory(n, seed=4)]
-    for e in envs:
-        e.reset()
-    out = envs[1].alloc_host_outputs()
-    for _ in range(4):
-        act = rng.uniform(-lim, lim, size=(n, 6)).astype(np.float32)
-        obs, reward, done, info = envs[0].step(torch.tensor(act, device='cuda'))
-        torch.cuda.synchronize()
-        envs[1].step_host(np.ascontiguousarray(act.T), out)
-        assert np.array_equal(out['observation'].T, obs['observation'].cpu().numpy())
-        assert np.array_equal(out['achieved_goal'].T, obs['achieved_goal'].cpu().numpy())
-        assert np.array_equal(out['desired_goal'].T, obs['desired_goal'].cpu().numpy())
-        assert np.array_equal(out['reward'], reward.cpu().numpy()) and np.array_equal(out['done'], done.cpu().numpy())
-        assert np.array_equal(out['is_success'], info['is_success'].cpu().numpy().astype(np.uint8))
-        assert np.array_equal(out['error'], info['error'].cpu().numpy())
-    for k in ('joints', 'episode', 't', 'desired_joints'):
-        assert torch.equal(envs[0].buffer(k), envs[1].buffer(k)), k
+    for late in ('1', '0'):
+        monkeypatch.setenv('CTR_HOST_FLAGS_LATE', late)          # read by ctr_create
+        envs = [vec_factory(n, seed=4), vec_factory(n, seed=4)]
+        for e in envs:
+            e.reset()
+        out = envs[1].alloc_host_outputs()
+        for _ in range(4):
+            act = rng.uniform(-lim, lim, size=(n, 6)).astype(np.float32)
+            obs, reward, done, info = envs[0].step(torch.tensor(act, device='cuda'))
+            torch.cuda.synchronize()
+            envs[1].step_host(np.ascontiguousarray(act.T), out)
+            assert np.array_equal(out['observation'].T, obs['observation'].cpu().numpy())
+            assert np.array_equal(out['achieved_goal'].T, obs['achieved_goal'].cpu().numpy())
+            assert np.array_equal(out['desired_goal'].T, obs['desired_goal'].cpu().numpy())
+            assert np.array_equal(out['reward'], reward.cpu().numpy()) and np.array_equal(out['done'], done.cpu().numpy())
+            assert np.array_equal(out['is_success'], info['is_success'].cpu().numpy().astype(np.uint8))
+            assert np.array_equal(out['error'], info['error'].cpu().numpy())
+        for k in ('joints', 'episode', 't', 'desired_joints'):
+            assert torch.equal(envs[0].buffer(k), envs[1].buffer(k)), k
 
 
 def test_backbone_shape_vs_reference_and_oracle(golden, oracle_c, tube_constants, vec_factory):
