@@ -46,7 +46,13 @@ constexpr int HER_PAD = HER_REC + 1;         // shared-memory row stride (odd: t
 #define CTR_HER_MLP 4
 #endif
 constexpr int HER_MLP = CTR_HER_MLP;         // records a warp loads per batch in k_her_sample (power of two <= 32)
-constexpr int HER_WARPS = 2;                 // warps per sampling block: 2 x 32 x 45 x 8 B = 23 KB of shared memory
+constexpr int HER_WARPS = 2;
+// batch rows are written once and read by another kernel later: streaming stores (evict-first) keep them from displacing ring lines in L2
+#ifndef CTR_HER_PLAIN_STORES
+#define HER_ST(p, v) __stcs((p), (v))
+#else
+#define HER_ST(p, v) (*(p) = (v))
+#endif                 // warps per sampling block: 2 x 32 x 45 x 8 B = 23 KB of shared memory
 
 // One warp per 32 environments.  Phase 1 (lane = env): the env's SoA rows are read coalesced, the record is assembled in
 // shared memory, cur_* move on to the post-step state, the episode counters are updated.  Phase 2: the warp writes the 32
@@ -191,19 +197,19 @@ __global__ void __launch_bounds__(32 * HER_WARPS) k_her_sample(const ctr_her_rin
             o = __dsub_rn(goal[d - 9], ach[d - 9]);               // obs.py:158: desired - achieved
             o2 = __dsub_rn(goal[d - 9], nach[d - 9]);
         }
-        b.obs[(int64_t)d * M + i] = o;
-        b.next_obs[(int64_t)d * M + i] = o2;
+        HER_ST(b.obs + (int64_t)d * M + i, o);
+        HER_ST(b.next_obs + (int64_t)d * M + i, o2);
     }
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-        b.achieved[(int64_t)c * M + i] = ach[c];
-        b.next_achieved[(int64_t)c * M + i] = nach[c];
-        b.desired[(int64_t)c * M + i] = goal[c];
+        HER_ST(b.achieved + (int64_t)c * M + i, ach[c]);
+        HER_ST(b.next_achieved + (int64_t)c * M + i, nach[c]);
+        HER_ST(b.desired + (int64_t)c * M + i, goal[c]);
     }
     const float* act = reinterpret_cast<const float*>(me + 2 * D + 10);
 #pragma unroll
-    for (int a = 0; a < 6; ++a) b.action[(int64_t)a * M + i] = act[a];
-    b.reward[i] = reward;
+    for (int a = 0; a < 6; ++a) HER_ST(b.action + (int64_t)a * M + i, act[a]);
+    HER_ST(b.reward + i, reward);
     b.done[i] = done;
     b.src[i] = col;
     b.goal_src[i] = gcol;
