@@ -1052,6 +1052,7 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     for (int s = 0; s < cfg->n_systems; ++s)
         for (int i = 0; i < 3; ++i)
             if (cfg->tube[s][i][7] != 0.0) h->all_uy_zero = 0;
+    if (getenv("CTR_NO_UY0")) h->all_uy_zero = 0;   // A/B switch: force the generic U_y instantiation (read once, here)
     const int64_t N = n_envs, D = h->obs_dim;
     int rc = 0;
     rc |= dev_alloc(h, &h->sys_dev, CTR_MAX_SYSTEMS);
@@ -1335,7 +1336,7 @@ static int launch_step_range(ctr_handle* h, KArgs a, const float* action_dev, in
     a.env_count = count;
     a.refill_blocks = refill_blocks;
     // U_y == 0 fast path: nominal tubes only (explicit per-env constants may carry any U_y)
-    const bool uy0 = h->all_uy_zero && !h->use_params && !getenv("CTR_NO_UY0");
+    const bool uy0 = h->all_uy_zero && !h->use_params;
 #ifndef CTR_DEBUG_SKIP_STEP_KERNEL      // measurement-only build: the host pipeline's copies without its kernels
     DISPATCH_STEP(uy0, h->cfg.integrator, h->cfg.precision,
                   <<<grid_for(count) + refill_blocks, BLOCK, 0, st>>>(a, action_dev));
@@ -1734,7 +1735,7 @@ int ctr_fk_shape(ctr_handle* h, const double* joints_dev, const int32_t* system_
     if (max_pts < 1) CTR_FAIL("max_pts must be >= 1");
     if (n <= 0) return 0;
     CTR_CUDA(cudaSetDevice(h->device));
-    if (h->all_uy_zero && !params_dev && !getenv("CTR_NO_UY0"))
+    if (h->all_uy_zero && !params_dev)
         k_fk_shape<true><<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(h->sys_dev, h->cfg.n_systems, joints_dev, system_dev, params_dev, n,
                                                                          h->cfg.rtol, h->cfg.atol, max_pts, shape_dev, npts_dev,
                                                                          tip_idx_dev, tip_dev, h->p.stats);
