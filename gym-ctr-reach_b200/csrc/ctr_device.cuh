@@ -41,23 +41,18 @@ struct LaneId {
 };
 
 // ---- lane exchange -------------------------------------------------------------------------------------------
-// CTR_XCH_SMEM = 1 routes the lane exchanges of rhs() and group_sum() through a per-warp shared-memory mailbox
-// (STS / __syncwarp / LDS) instead of __shfl_sync: a 64-bit shuffle is two SHFL.IDX whose halves ptxas then moves into an
-// aligned register pair (112 of the 941 instructions of one Dormand-Prince attempt were such copies).  Same values, same
-// order of operations: results are bit-identical between the two settings.
+// The lane exchanges of rhs() and group_sum() go through a per-warp shared-memory mailbox (STS / __syncwarp / LDS), not
+// __shfl_sync: a 64-bit shuffle is two SHFL.IDX whose halves ptxas then moves into an aligned register pair (112 of the 941
+// instructions of one Dormand-Prince attempt were such copies in the shuffle build of round 1, profiles/r1r_*).
 #ifndef CTR_BLOCK
 #define CTR_BLOCK 128
 #endif
-#ifndef CTR_XCH_SMEM
-#define CTR_XCH_SMEM 1
-#endif
-#if CTR_XCH_SMEM
-// Mailbox: three rows of value PAIRS (one STS.128 / LDS.128 each in float64) and one row of single values per warp.
+// Mailbox: rows of value PAIRS (one STS.128 / LDS.128 each in float64).
 template <typename T>
 struct alignas(2 * sizeof(T)) XPair {
     T a, b;
 };
-// rows: (uz, angle) | (cos, sin) | (ux, uy) | (group_sum partial, -).  All four share one base register per lane, the row is an
+// rows: (uz, angle) | (cos, sin) | (ux, uy) | (group_sum partials).  All four share one base register per lane, the row is an
 // immediate offset; 34 entries per row so that l0 + 2 of the idle lanes 30 / 31 stays inside the row's storage.
 __shared__ XPair<double> s_xp[CTR_BLOCK / 32][4][34];
 template <typename T>
@@ -76,7 +71,6 @@ template <typename T>
 __device__ __forceinline__ T xch_get2b(const LaneId& id, int row, int lane) {
     return reinterpret_cast<const XPair<T>*>(&s_xp[id.w][row][0])[lane].b;
 }
-#endif
 
 __device__ __forceinline__ LaneId lane_id() {
     LaneId id;
@@ -98,18 +92,22 @@ __device__ __forceinline__ T pick3(int j, T a0, T a1, T a2) {
 // (p0 + p1) + p2 of the three lanes' partials, identical bits on all three lanes.
 template <typename T>
 __device__ __forceinline__ T group_sum(const LaneId& id, T p) {
-#if CTR_XCH_SMEM
     __syncwarp();              // the previous round's readers of the row are done
     reinterpret_cast<XPair<T>*>(&s_xp[id.w][3][0])[id.lane].a = p;
     __syncwarp();
     const XPair<T>* row = reinterpret_cast<const XPair<T>*>(&s_xp[id.w][3][0]) + id.l0;
     const T p0 = row[0].a, p1 = row[1].a, p2 = row[2].a;
-#else
-    T p0 = __shfl_sync(FULL, p, id.l0);
-    T p1 = __shfl_sync(FULL, p, id.l0 + 1);
-    T p2 = __shfl_sync(FULL, p, id.l0 + 2);
-#endif
     return (p0 + p1) + p2;
+}
+// two sums in one exchange
+template <typename T>
+__device__ __forceinline__ void group_sum2(const LaneId& id, T& p, T& q) {
+    __syncwarp();
+    xch_put2(id, 3, p, q);
+    __syncwarp();
+    const XPair<T> r0 = xch_get2<T>(id, 3, id.l0), r1 = xch_get2<T>(id, 3, id.l0 + 1), r2 = xch_get2<T>(id, 3, id.l0 + 2);
+    p = (r0.a + r1.a) + r2.a;
+    q = (r0.b + r1.b) + r2.b;
 }
 
 // ---- math helpers, overloaded on the state type --------------------------------------------------------------
@@ -124,8 +122,10 @@ __device__ __forceinline__ float max_t(float a, float b) { return fmaxf(a, b); }
 // every caller sits on a path where a NaN already marks the solve as failed (rk.py:129-130 analogue in fk_dp45).
 __device__ __forceinline__ double dmin(double a, double b) { return a < b ? a : b; }
 __device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
-__device__ __forceinline__ double maxabs_t(double a, double b) { return dmax(fabs(a), fabs(b)); }
-__device__ __forceinline__ float maxabs_t(float a, float b) { return fmaxf(fabsf(a), fabsf(b)); }
+// the operand of larger magnitude, sign included: the caller applies |.| inside its FMA, where it is a free operand modifier
+// (one DSETP on |a|, |b| and two selects instead of materialising both absolute values first)
+__device__ __forceinline__ double absmax_arg(double a, double b) { return fabs(a) > fabs(b) ? a : b; }
+__device__ __forceinline__ float absmax_arg(float a, float b) { return fabsf(a) > fabsf(b) ? a : b; }
 
 // 1/x for normal positive x: MUFU.RCP64H seed + two Newton steps (relative error < 2^-52; no special cases, no
 // slow-path call -- the compiler's '/' costs ~3x as much and a branch).
@@ -155,7 +155,8 @@ __device__ __forceinline__ double rcp_t(double a) { return rcp_1n(a); }
 #endif
 __device__ __forceinline__ float rcp_t(float a) { return 1.0f / a; }
 
-// sqrt(x) for normal positive x (MUFU.RSQ64H seed + Goldschmidt, final residual correction)
+// sqrt(x) for normal positive x: MUFU.RSQ64H seed (2^-20), one Goldschmidt iteration (2^-40), residual correction
+// (error squares again: correctly rounded in all but ~1e-7 of the arguments, 1 ulp there; scripts/rcp_probe.cu)
 __device__ __forceinline__ double sqrt_fast(double x) {
     double y;
     asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
@@ -163,20 +164,25 @@ __device__ __forceinline__ double sqrt_fast(double x) {
     double r = fma(-h, g, 0.5);
     g = fma(g, r, g);
     h = fma(h, r, h);
-    r = fma(-h, g, 0.5);
-    g = fma(g, r, g);
-    h = fma(h, r, h);
     r = fma(-g, g, x);
     return fma(r, h, g);
 }
 
-// x^(-1/10) for x in [1e-30, 1e30]: float MUFU seed (lg2/ex2, ~1e-6) + two Newton steps on y^-10 = x
-// (y <- y (1 + (1 - x y^10) / 10), error -> 5.5 e^2), i.e. full double precision in 14 FP64 ops.  Replaces the
-// pow(err, -0.2) / pow(., 0.2) of the step-size controller (rk.py:147, common.py:127), whose argument is err^2 here.
+// x^(-1/10) for x in [1e-30, 1e30]: float MUFU seed (lg2/ex2, ~1e-6) + NEWTON steps on y^-10 = x
+// (y <- y (1 + (1 - x y^10) / 10), error -> 5.5 e^2): 5.5e-12 after one step, full double precision after two.  Replaces
+// the pow(err, -0.2) / pow(., 0.2) of the step-size controller (rk.py:147, common.py:127), whose argument is err^2 here.
+// One step is what the controller needs: a relative 5.5e-12 in the next step size moves the next error norm by ~3e-11,
+// i.e. it can flip an accept / reject decision only when that norm lies within 3e-11 of 1 -- the same order as the
+// 9.9e-13 of rcp_1n below and far below the tip tolerance either way (a flipped decision moves a tip by < 3e-5 m).
+// The float seed is clamped to [1e-30, 1e30] (two FMNMX); the Newton step runs on the unclamped x.  Outside that range
+// the result is only used through the controller's own limits (rk.py:10-11 MIN_FACTOR / MAX_FACTOR), which saturate long
+// before: x < 1e-30 gives > 1000, x > 1e30 a value below 1e-3 (possibly negative: it meets max(., 0.2) next).
+template <int NEWTON>
 __device__ __forceinline__ double pow_m01(double x) {
-    double y = (double)exp2f(-0.1f * __log2f((float)x));
+    const float xf = fminf(fmaxf((float)x, 1e-30f), 1e30f);
+    double y = (double)exp2f(-0.1f * __log2f(xf));
 #pragma unroll
-    for (int k = 0; k < 2; ++k) {
+    for (int k = 0; k < NEWTON; ++k) {
         double y2 = y * y, y4 = y2 * y2, y8 = y4 * y4, y10 = y8 * y2;
         double e = fma(-x, y10, 1.0);
         y = fma(y * 0.1, e, y);
@@ -184,15 +190,15 @@ __device__ __forceinline__ double pow_m01(double x) {
     return y;
 }
 
-// sin / cos of a double with a 3-term Cody-Waite reduction (exact first product for |n| < 2^20) and the fdlibm
+// sin / cos of a double with a 2-term Cody-Waite reduction (exact first product for |n| < 2^20) and the fdlibm
 // kernel polynomials on [-pi/4, pi/4]; <= 1 ulp for |x| < 1e3, <= 2 ulp up to 1e5; larger arguments take the
 // library path (out of line, so the hot loop carries only a compare and a never-taken branch).  21 FP64 ops.
 __device__ __noinline__ void sincos_slow(double x, double* s, double* c) { sincos(x, s, c); }
 
 #define TC(i, v) c_trig[i]
 __constant__ double c_trig[16] = {
-    0.63661977236758138243, 6755399441055744.0, 1.57079632673412561417e+00, 6.07710050630396597660e-11,
-    2.02226624871116645580e-21, 1.58969099521155010221e-10, -2.50507602534068634195e-08, -1.13596475577881948265e-11,
+    0.63661977236758138243, 6755399441055744.0, 1.57079632673412561417e+00, 6.07710050650619224932e-11,
+    0.0, 1.58969099521155010221e-10, -2.50507602534068634195e-08, -1.13596475577881948265e-11,
     2.08757232129817482790e-09, 2.75573137070700676789e-06, -2.75573143513906633035e-07, -1.98412698298579493134e-04,
     2.48015872894767294178e-05, 8.33333333332248946124e-03, -1.38888888888741095749e-03, -1.66666666666666324348e-01};
 
@@ -208,9 +214,10 @@ __device__ __forceinline__ void sincos_t(double x, double* s, double* c) {
     const double t = fma(x, TC(0, 0.63661977236758138243), TC(1, 6755399441055744.0));
     const int q = __double2loint(t);
     const double n = t - TC(1, 6755399441055744.0);
+    // two-term Cody-Waite: n * pio2_1 (33 bits x < 2^20) is exact and so is x - n pio2_1 (Sterbenz); pio2_1t is the rest of
+    // pi/2 rounded to double, its error times n stays below 1e-21
     double r = fma(-n, TC(2, 1.57079632673412561417e+00), x);
-    r = fma(-n, TC(3, 6.07710050630396597660e-11), r);
-    r = fma(-n, TC(4, 2.02226624871116645580e-21), r);
+    r = fma(-n, TC(3, 6.07710050650619224932e-11), r);
     const double z = r * r;
     double ps = fma(z, TC(5, 1.58969099521155010221e-10), TC(6, -2.50507602534068634195e-08));
     double pc = fma(z, TC(7, -1.13596475577881948265e-11), TC(8, 2.08757232129817482790e-09));
@@ -222,8 +229,9 @@ __device__ __forceinline__ void sincos_t(double x, double* s, double* c) {
     pc = fma(z, pc, TC(14, -1.38888888888741095749e-03));
     ps = fma(z, ps, TC(15, -1.66666666666666324348e-01));
     pc = fma(z, pc, 4.16666666666666019037e-02);
+    pc = fma(z, pc, -0.5);
     double sn = fma(r * z, ps, r);
-    double cs = fma(z * z, pc, fma(z, -0.5, 1.0));
+    double cs = fma(z, pc, 1.0);
 #ifdef CTR_TRIG_FP_SIGN
     if (q & 1) {
         const double tmp = sn;
@@ -386,18 +394,15 @@ struct Section {
     T An, Bn;   // tube (j+1)%3
     T Ap, Bp;   // tube (j+2)%3
     T kx, ky;   // (EI_j / GJ_j) * Ux_j , (EI_j / GJ_j) * Uy_j   (0 when tube j is absent or straight: model.py:97-101)
-    T present;  // 1 when tube j exists on this section (alpha_j' = uz_j), else 0
+    bool present;  // tube j exists on this section (alpha_j' = uz_j), else alpha_j' = 0
 };
 
 // ---- ODE right-hand side (model.py:72-117), one lane's slice ------------------------------------------------
 // Y = {uz_j, alpha_j, r_j, R_j0, R_j1, R_j2} -> D = d/ds of the same.  Executed by the full warp.
-// tg keeps the sin / cos of the two angle differences this lane uses: when a new section starts at the state the
-// last evaluation was made at (FSAL), only the algebra is redone with the new constants (do_trig = false).
-template <typename T>
-struct Trig {
-    T co, so;   // cos / sin(alpha_j - alpha_{j+1})
-    T cp, sp;   // cos / sin(alpha_{j-1} - alpha_j)
-};
+// The sin / cos of the two angle differences a lane uses -- (co, so) of alpha_j - alpha_{j+1}, computed by the lane, and
+// (cp, sp) of alpha_{j-1} - alpha_j, computed by lane j-1 -- stay in row 1 of the mailbox after every call.  When a new
+// section starts at the state the last evaluation was made at (FSAL), only the algebra is redone with the new constants:
+// do_trig = false re-reads the row instead of carrying four doubles per lane through the whole integration loop.
 
 // The twist integrates to a few radians at most, so the argument range of the sincos is decided once per FK from the
 // initial angle differences: true when some environment of this warp needs the library (large-argument) path.
@@ -409,61 +414,49 @@ __device__ __forceinline__ bool needs_slow_trig(int j, const double* alpha) {
 // UY0: every tube has y_curvature == 0 (all four systems of the reference, __init__.py:9-70; domain randomisation never
 // touches U_y, model_utils.py:12-20): the B terms and ky vanish -- 5 FP64 operations and 4 registers less per call.
 template <typename T, bool SLOW, bool UY0>
-__device__ __forceinline__ void rhs(const LaneId& id, const Section<T>& sc, bool do_trig, Trig<T>& tg, const T (&Y)[6],
-                                    T (&D)[6]) {
-#if CTR_XCH_SMEM
+__device__ __forceinline__ void rhs(const LaneId& id, const Section<T>& sc, bool do_trig, const T (&Y)[6], T (&D)[6]) {
     // Pair rows 0 | 1 | 2 are written in that order with a warp barrier after each, and every read of a row sits before the
     // barrier that precedes the row's next write (uz_0 of row 0 is therefore fetched before the last barrier of the call).
     xch_put2(id, 0, Y[0], Y[1]);
     __syncwarp();
+    T co, so;
     if (do_trig) {   // warp-uniform
         const T a_next = xch_get2b<T>(id, 0, id.lnext);
-        sincos_t<SLOW>(Y[1] - a_next, &tg.so, &tg.co);
-        xch_put2(id, 1, tg.co, tg.so);
+        sincos_t<SLOW>(Y[1] - a_next, &so, &co);
+        xch_put2(id, 1, co, so);
         __syncwarp();
-        const XPair<T> pr = xch_get2<T>(id, 1, id.lprev);
-        tg.cp = pr.a;
-        tg.sp = pr.b;
+    } else {
+        const XPair<T> own = xch_get2<T>(id, 1, id.lane);
+        co = own.a;
+        so = own.b;
     }
-#else
-    if (do_trig) {   // warp-uniform
-        const T a_next = __shfl_sync(FULL, Y[1], id.lnext);
-        sincos_t<SLOW>(Y[1] - a_next, &tg.so, &tg.co);
-        tg.cp = __shfl_sync(FULL, tg.co, id.lprev);
-        tg.sp = __shfl_sync(FULL, tg.so, id.lprev);
-    }
-#endif
+    const XPair<T> pr = xch_get2<T>(id, 1, id.lprev);
+    const T cp = pr.a, sp = pr.b;
     // model.py:87-94 with cos(0) = 1, sin(0) = 0 folded; sin(alpha_j - alpha_{j-1}) = -sp
     T ux, uy;
     if (UY0) {
-        ux = fma_t(sc.An, tg.co, sc.Ao);
-        uy = -sc.An * tg.so;
-        ux = fma_t(sc.Ap, tg.cp, ux);
-        uy = fma_t(sc.Ap, tg.sp, uy);
+        ux = fma_t(sc.An, co, sc.Ao);
+        uy = -sc.An * so;
+        ux = fma_t(sc.Ap, cp, ux);
+        uy = fma_t(sc.Ap, sp, uy);
         D[0] = -(uy * sc.kx);                                // model.py:101 with U_y = 0
     } else {
-        ux = fma_t(sc.An, tg.co, sc.Ao);
-        uy = fma_t(-sc.An, tg.so, sc.Bo);
-        ux = fma_t(sc.Bn, tg.so, ux);
-        uy = fma_t(sc.Bn, tg.co, uy);
-        ux = fma_t(sc.Ap, tg.cp, ux);
-        uy = fma_t(sc.Ap, tg.sp, uy);
-        ux = fma_t(-sc.Bp, tg.sp, ux);
-        uy = fma_t(sc.Bp, tg.cp, uy);
+        ux = fma_t(sc.An, co, sc.Ao);
+        uy = fma_t(-sc.An, so, sc.Bo);
+        ux = fma_t(sc.Bn, so, ux);
+        uy = fma_t(sc.Bn, co, uy);
+        ux = fma_t(sc.Ap, cp, ux);
+        uy = fma_t(sc.Ap, sp, uy);
+        ux = fma_t(-sc.Bp, sp, ux);
+        uy = fma_t(sc.Bp, cp, uy);
         D[0] = fma_t(ux, sc.ky, -(uy * sc.kx));              // model.py:101  (0 when absent: kx = ky = 0)
     }
-    D[1] = sc.present * Y[0];                            // model.py:99,102
-#if CTR_XCH_SMEM
+    D[1] = sc.present ? Y[0] : (T)0;                         // model.py:99,102
     const T uz0 = xch_get2a<T>(id, 0, id.l0);
     xch_put2(id, 2, ux, uy);
     __syncwarp();
     const XPair<T> u0 = xch_get2<T>(id, 2, id.l0);
     const T ux0 = u0.a, uy0 = u0.b;
-#else
-    const T ux0 = __shfl_sync(FULL, ux, id.l0);
-    const T uy0 = __shfl_sync(FULL, uy, id.l0);
-    const T uz0 = __shfl_sync(FULL, Y[0], id.l0);
-#endif
     D[2] = Y[5];                                         // r' = R e3          (model.py:108)
     D[3] = fma_t(Y[4], uz0, -(Y[5] * uy0));              // R' = R u_hat, row j (model.py:107,109)
     D[4] = fma_t(Y[5], ux0, -(Y[3] * uz0));
@@ -525,7 +518,7 @@ __device__ __forceinline__ bool advance_section(const GroupScratch& gs, const do
     sc.Bp = (T)(cp ? der[DER_EIUY + mp] * inv : 0.0);
     sc.kx = (T)(co ? der[DER_KX + mo] : 0.0);
     sc.ky = (T)(co ? der[DER_KY + mo] : 0.0);
-    sc.present = ((pat >> mo) & 1) ? (T)1 : (T)0;
+    sc.present = ((pat >> mo) & 1) != 0;
     return true;
 }
 
@@ -534,6 +527,11 @@ __device__ __forceinline__ bool advance_section(const GroupScratch& gs, const do
 // SHAPE: additionally sample r_j at the 30 abscissae of every section through scipy's dense output (rk.py RkDenseOutput:
 // y_old + h * Q . [x, x^2, x^3, x^4], Q = K^T P, x = (s - t_old) / h), as solve_ivp(t_eval=...) does for Model.r
 // (model.py:143-158, ivp.py t_eval handling: the samples in (t_old, t_new] after every accepted step).
+//
+// Register budget (128 per thread at 4 blocks / SM): y, f, k2..k6 and the stage argument are 8 x 6 doubles = 96 registers, so
+// everything else that lives across the loop is kept minimal: the loop counts attempts, rejections and started sections
+// only (nfev = 6 attempts + 2 started + zero-length spans is derived at the end), the trigonometry of the last evaluation
+// stays in the mailbox (rhs), `present` is a predicate.
 template <typename T, bool SLOW, bool UY0, bool SHAPE = false>
 __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const GroupScratch& gs, const double* der,
                                         const double* alpha, double rtol_d, double atol_d, T (&y)[6], FkInfo& info,
@@ -543,20 +541,16 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
     initial_state<T>(j, alpha, y);
     const int packed = valid ? gs.nsec : 0;
     const int nsec = packed & 0xff;
-    info.nfev = info.nsec = packed >> 8;          // zero-length spans: one RHS call each, no step
-    info.nacc = info.nrej = info.failed = 0;
     const T rtol = (T)rtol_d, atol = (T)atol_d;
     Section<T> sc;
-    sc.Ao = sc.Bo = sc.An = sc.Bn = sc.Ap = sc.Bp = sc.kx = sc.ky = sc.present = (T)0;
-    Trig<T> tg;
-    tg.co = tg.cp = (T)1;
-    tg.so = tg.sp = (T)0;
+    sc.Ao = sc.Bo = sc.An = sc.Bn = sc.Ap = sc.Bp = sc.kx = sc.ky = (T)0;
+    sc.present = false;
     T f[6];
 #pragma unroll
     for (int i = 0; i < 6; ++i) f[i] = (T)0;
-    int ksec = 0, attempts = 0;
+    int ksec = 0, attempts = 0, nrej = 0;
     double t = 0.0, tf = 0.0, h_abs = 0.0;
-    bool done = !valid, need_sec = true, rejected = false;
+    bool done = !valid, need_sec = true, rejected = false, failed = false;
     bool first = true;   // warp-uniform: no RHS has been evaluated yet, so slot 0 needs the trigonometry
     int sh_i = SHAPE_SAMPLES, sh_sec = -1;          // SHAPE: next abscissa of the current section, sections started
     double sh_a = 0.0, sh_step = 0.0;
@@ -570,7 +564,6 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
                 if (init) {
                     need_sec = false;
                     rejected = false;
-                    info.nsec += 1;
                     if (SHAPE) {
                         sh_a = t;
                         sh_step = __ddiv_rn(__dsub_rn(tf, t), (double)(SHAPE_SAMPLES - 1));
@@ -588,7 +581,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
         //      whenever at least one environment starts a section (its FSAL derivative belongs to the old constants)
         if (any_init) {
             T D[6], rs[6], Y[6];
-            rhs<T, SLOW, UY0>(id, sc, first, tg, y, D);                // f0 = f(t0, y0); trigonometry reused unless first
+            rhs<T, SLOW, UY0>(id, sc, first, y, D);                    // f0 = f(t0, y0); trigonometry reused unless first
             T p0 = 0, p1 = 0;
 #pragma unroll
             for (int i = 0; i < 6; ++i) {
@@ -598,30 +591,28 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
                 p0 = fma_t(a, a, p0);
                 p1 = fma_t(b, b, p1);
             }
-            const double m0 = (double)group_sum(id, p0) * (1.0 / 18.0);   // d0^2 (common.py:63-65 RMS norm)
-            const double m1 = (double)group_sum(id, p1) * (1.0 / 18.0);   // d1^2
+            group_sum2(id, p0, p1);
+            const double m0 = (double)p0 * (1.0 / 18.0);                  // d0^2 (common.py:63-65 RMS norm)
+            const double m1 = (double)p1 * (1.0 / 18.0);                  // d1^2
             const double interval = fabs(tf - t);
-            double h0 = (m0 < 1e-10 || m1 < 1e-10) ? 1e-6 : 0.01 * sqrt_fast(m0 * rcp_fast(m1));
+            double h0 = (m0 < 1e-10 || m1 < 1e-10) ? 1e-6 : 0.01 * sqrt_fast(m0 * rcp_1n(m1));
             h0 = dmin(h0, interval);
             const T h0t = (T)h0;
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(h0t, f[i], y[i]);   // common.py:113
             T D1[6];
-            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, D1);
+            rhs<T, SLOW, UY0>(id, sc, true, Y, D1);
             T p2 = 0;
 #pragma unroll
             for (int i = 0; i < 6; ++i) {
                 const T c = (D1[i] - f[i]) * rs[i];
                 p2 = fma_t(c, c, p2);
             }
-            const double m2 = (double)group_sum(id, p2) * (1.0 / 18.0) * rcp_fast(h0 * h0);   // d2^2
+            const double m2 = (double)group_sum(id, p2) * (1.0 / 18.0) * rcp_1n(h0 * h0);   // d2^2
             const double M = dmax(m1, m2);
             // h1 = (0.01 / max(d1, d2))^(1/5) = (1e4 M)^(-1/10)
-            const double h1 = (M <= 1e-30) ? dmax(1e-6, h0 * 1e-3) : pow_m01(dmin(dmax(M * 1e4, 1e-30), 1e30));
-            if (init) {
-                h_abs = dmin(dmin(100.0 * h0, h1), interval);
-                info.nfev += 2;
-            }
+            const double h1 = (M <= 1e-30) ? dmax(1e-6, h0 * 1e-3) : pow_m01<1>(M * 1e4);
+            if (init) h_abs = dmin(dmin(100.0 * h0, h1), interval);
         }
 
         // ---- one step attempt (rk.py:108-178)
@@ -637,26 +628,26 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
             const T c1 = h * dpc<T>(A21);
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(c1, f[i], y[i]);
-            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, k2);
+            rhs<T, SLOW, UY0>(id, sc, true, Y, k2);
         }
         {
             const T c1 = h * dpc<T>(A31), c2 = h * dpc<T>(A32);
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(c2, k2[i], fma_t(c1, f[i], y[i]));
-            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, k3);
+            rhs<T, SLOW, UY0>(id, sc, true, Y, k3);
         }
         {
             const T c1 = h * dpc<T>(A41), c2 = h * dpc<T>(A42), c3 = h * dpc<T>(A43);
 #pragma unroll
             for (int i = 0; i < 6; ++i) Y[i] = fma_t(c3, k3[i], fma_t(c2, k2[i], fma_t(c1, f[i], y[i])));
-            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, k4);
+            rhs<T, SLOW, UY0>(id, sc, true, Y, k4);
         }
         {
             const T c1 = h * dpc<T>(A51), c2 = h * dpc<T>(A52), c3 = h * dpc<T>(A53), c4 = h * dpc<T>(A54);
 #pragma unroll
             for (int i = 0; i < 6; ++i)
                 Y[i] = fma_t(c4, k4[i], fma_t(c3, k3[i], fma_t(c2, k2[i], fma_t(c1, f[i], y[i]))));
-            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, k5);
+            rhs<T, SLOW, UY0>(id, sc, true, Y, k5);
         }
         {
             const T c1 = h * dpc<T>(A61), c2 = h * dpc<T>(A62), c3 = h * dpc<T>(A63), c4 = h * dpc<T>(A64),
@@ -664,7 +655,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
 #pragma unroll
             for (int i = 0; i < 6; ++i)
                 Y[i] = fma_t(c5, k5[i], fma_t(c4, k4[i], fma_t(c3, k3[i], fma_t(c2, k2[i], fma_t(c1, f[i], y[i])))));
-            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, k6);
+            rhs<T, SLOW, UY0>(id, sc, true, Y, k6);
         }
         T e5[6];   // the k1..k6 part of the error estimate (k2 has weight 0); k2..k5 die here
         {
@@ -675,30 +666,26 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
                 e5[i] = fma_t(dpc<T>(E6), k6[i], fma_t(dpc<T>(E5), k5[i], fma_t(dpc<T>(E4), k4[i],
                               fma_t(dpc<T>(E3), k3[i], dpc<T>(E1) * f[i]))));
             }
-            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, k7);                // f(t + h, y_new)
+            rhs<T, SLOW, UY0>(id, sc, true, Y, k7);                    // f(t + h, y_new)
         }
         // ---- error norm and step-size control (rk.py:139-159)
         T pe = 0;
 #pragma unroll
         for (int i = 0; i < 6; ++i) {
             const T e = fma_t(dpc<T>(E7), k7[i], e5[i]);
-            const T sc_i = fma_t(maxabs_t(y[i], Y[i]), rtol, atol);                  // rk.py:141
+            const T sc_i = fma_t(abs_t(absmax_arg(y[i], Y[i])), rtol, atol);         // rk.py:141
             const T q = e * rcp_t(sc_i);
             pe = fma_t(q, q, pe);
         }
         const double m = (double)group_sum(id, pe) * (h_d * h_d) * (1.0 / 18.0);    // error_norm^2 (rk.py:142)
         const bool accept = m < 1.0;                                                // rk.py:144
-        const double fac = 0.9 * pow_m01(dmin(dmax(m, 1e-14), 1e10));               // SAFETY * norm^(-1/5)
-        double factor;
-        if (accept) {
-            factor = (m == 0.0) ? 10.0 : dmin(fac, 10.0);                           // rk.py:145-149
-            if (rejected) factor = dmin(factor, 1.0);                               // rk.py:151-152
-        } else {
-            factor = dmax(fac, 0.2);                                                // rk.py:157-158
-        }
+        // rk.py:145-158: accepted: min(MAX_FACTOR, SAFETY norm^-1/5), at most 1 after a rejection; rejected: max(MIN_FACTOR, .).
+        // One expression serves both: an accepted step has fac > 0.9 (the lower limit is idle), a rejected one fac <= 0.9 (the
+        // upper limit is idle); norm == 0 gives fac > 900, i.e. MAX_FACTOR as rk.py:146 states it; a NaN fac gives MIN_FACTOR.
+        const double fac = 0.9 * pow_m01<1>(m);                                     // SAFETY * norm^(-1/5)
+        const double factor = dmin(dmax(fac, 0.2), rejected ? 1.0 : 10.0);
         if (active) {
             attempts += 1;
-            info.nfev += 6;
             h_abs *= factor;
             if (accept) {
                 if (SHAPE) {
@@ -736,24 +723,31 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
                     f[i] = k7[i];                                                   // FSAL (rk.py:170)
                 }
                 t = t_new;
-                info.nacc += 1;
                 rejected = false;
                 if (t == tf) need_sec = true;
             } else {
                 rejected = true;
-                info.nrej += 1;
+                nrej += 1;
                 if (h_abs < min_step || !(m == m)) {   // rk.py:129-130 TOO_SMALL_STEP; NaN state (model.py:69)
-                    info.failed = 1;
+                    failed = true;
                     done = true;
                 }
             }
             if (attempts >= MAX_ATTEMPTS) {
-                info.failed = 1;
+                failed = true;
                 done = true;
             }
         }
         first = false;
     }
+    // zero-length spans cost one RHS call each and no step (base.py); a started section costs 2 calls (select_initial_step),
+    // an attempt 6
+    const int skipped = packed >> 8;
+    info.nsec = skipped + ksec;
+    info.nfev = skipped + 2 * ksec + 6 * attempts;
+    info.nrej = nrej;
+    info.nacc = attempts - nrej;
+    info.failed = failed ? 1 : 0;
 }
 
 // INTEG 1: classical RK4, rk4_steps fixed steps per section (throughput mode; not the parity mode).
@@ -768,10 +762,8 @@ __device__ __forceinline__ void fk_rk4(const LaneId& id, bool valid, const Group
     info.nfev = info.nsec = packed >> 8;
     info.nacc = info.nrej = info.failed = 0;
     Section<T> sc;
-    sc.Ao = sc.Bo = sc.An = sc.Bn = sc.Ap = sc.Bp = sc.kx = sc.ky = sc.present = (T)0;
-    Trig<T> tg;
-    tg.co = tg.cp = (T)1;
-    tg.so = tg.sp = (T)0;
+    sc.Ao = sc.Bo = sc.An = sc.Bn = sc.Ap = sc.Bp = sc.kx = sc.ky = (T)0;
+    sc.present = false;
     int ksec = 0, steps_left = 0;
     double t = 0.0, tf = 0.0;
     T h = (T)0;
@@ -797,7 +789,7 @@ __device__ __forceinline__ void fk_rk4(const LaneId& id, bool valid, const Group
 #pragma unroll 1
         for (int s = 0; s < 4; ++s) {
             T D[6];
-            rhs<T, SLOW, UY0>(id, sc, true, tg, Y, D);
+            rhs<T, SLOW, UY0>(id, sc, true, Y, D);
             const T w = (s == 0 || s == 3) ? (T)(1.0 / 6.0) : (T)(1.0 / 3.0);
             const T c = (s == 2) ? h : h * (T)0.5;
 #pragma unroll

@@ -170,15 +170,16 @@ __device__ __forceinline__ double warp_sum(double v) {
 }
 
 // observation of one env written cooperatively by its 3 lanes (obs.py:136-164, obs_utils.py:41-53,69-80).
+// bf / af: the lane's own extension and rotation; bprev / aprev: those of tube j - 1 (0 for j == 0).
 // proprioceptive: trig of the float32 joints in float32.  egocentric: prop2ego's np.diff(..., prepend=0) promotes the
 // float32 joints to float64, so the first differences and the trig are float64 arithmetic.
-__device__ __forceinline__ void write_obs(double* obs, int64_t n, int64_t env, int j, const float (&q)[6], int rep,
-                                          double des_j, double ach_j, double tol, int system, int obs_dim) {
-    const float bf = pick3(j, q[0], q[1], q[2]), af = pick3(j, q[3], q[4], q[5]);
+__device__ __forceinline__ void write_obs(double* obs, int64_t n, int64_t env, int j, float bf, float af, float bprev,
+                                          float aprev, int rep, double des_j, double ach_j, double tol, int system,
+                                          int obs_dim) {
     double b, c, s;
     if (rep == CTR_REP_EGOCENTRIC) {
-        b = __dsub_rn((double)bf, (double)pick3(j, 0.f, q[0], q[1]));
-        const double a = __dsub_rn((double)af, (double)pick3(j, 0.f, q[3], q[4]));
+        b = __dsub_rn((double)bf, (double)bprev);
+        const double a = __dsub_rn((double)af, (double)aprev);
         sincos(a, &s, &c);
     } else {
         float sf, cf;
@@ -193,6 +194,11 @@ __device__ __forceinline__ void write_obs(double* obs, int64_t n, int64_t env, i
     obs[(int64_t)(9 + j) * n + env] = __dsub_rn(des_j, ach_j);
     if (j == 0) obs[(int64_t)12 * n + env] = tol;
     if (j == 1 && obs_dim > 13) obs[(int64_t)13 * n + env] = (double)system;
+}
+__device__ __forceinline__ void write_obs(double* obs, int64_t n, int64_t env, int j, const float (&q)[6], int rep,
+                                          double des_j, double ach_j, double tol, int system, int obs_dim) {
+    write_obs(obs, n, env, j, pick3(j, q[0], q[1], q[2]), pick3(j, q[3], q[4], q[5]), pick3(j, 0.f, q[0], q[1]),
+              pick3(j, 0.f, q[3], q[4]), rep, des_j, ach_j, tol, system, obs_dim);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -354,15 +360,26 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_step(const KArgs a, const
             act[i] = action[(int64_t)i * a.act_stride_field + e * a.act_stride_env];
         }
         set_action(q, act, sc, a.n_substeps);                                  // ctr_reach_env.py:134-135
+        // the new joints are final here: store them now and fetch the lane's own pair back after the solve, so that no
+        // joint value occupies a register across the integration loop (it runs at the 128-register limit)
+        if (valid) {
+            p.joints[(int64_t)j * n + env] = pick3(j, q[0], q[1], q[2]);
+            p.joints[(int64_t)(3 + j) * n + env] = pick3(j, q[3], q[4], q[5]);
+        }
 
         GroupScratch& gs = group_slot(s_gs, id);
-        double LL[6];
-        const double* der = env_consts(sc, p.tube_params, n, e, a.use_params != 0, j == 0, gs, LL);
-        double beta[3] = {(double)q[0], (double)q[1], (double)q[2]};           // model.py:50-51
-        double alpha[3] = {(double)q[3], (double)q[4], (double)q[5]};
         T y[6];
         FkInfo info;
-        fk_group<T, INTEG>(id, valid, gs, LL, LL + 3, der, beta, alpha, a.rtol, a.atol, a.rk4_steps, y, info);
+        {
+            double LL[6];
+            const double* der = env_consts(sc, p.tube_params, n, e, a.use_params != 0, j == 0, gs, LL);
+            double beta[3] = {(double)q[0], (double)q[1], (double)q[2]};           // model.py:50-51
+            double alpha[3] = {(double)q[3], (double)q[4], (double)q[5]};
+            fk_group<T, INTEG>(id, valid, gs, LL, LL + 3, der, beta, alpha, a.rtol, a.atol, a.rk4_steps, y, info);
+        }
+        const float bf = valid ? p.joints[(int64_t)j * n + env] : 0.f, af = valid ? p.joints[(int64_t)(3 + j) * n + env] : 0.f;
+        float bprev = __shfl_up_sync(FULL, bf, 1), aprev = __shfl_up_sync(FULL, af, 1);
+        if (j == 0) bprev = aprev = 0.f;
 
         // ---- reward / done / success / error (ctr_reach_env.py:138-140, 155-156, 168-170)
         const double ach_j = (double)y[2];
@@ -391,14 +408,12 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_step(const KArgs a, const
         episode = __shfl_sync(FULL, episode, id.l0);
 
         if (valid) {
-            p.joints[(int64_t)j * n + env] = pick3(j, q[0], q[1], q[2]);
-            p.joints[(int64_t)(3 + j) * n + env] = pick3(j, q[3], q[4], q[5]);
             p.achieved[(int64_t)j * n + env] = ach_j;
 #pragma unroll
             for (int c = 0; c < 3; ++c) p.orientation[(int64_t)(3 * j + c) * n + env] = (double)y[3 + c];
-            write_obs(p.obs, n, env, j, q, a.rep, des_j, ach_j, a.tol, sysid, a.obs_dim);
+            write_obs(p.obs, n, env, j, bf, af, bprev, aprev, a.rep, des_j, ach_j, a.tol, sysid, a.obs_dim);
             if (finish) {
-                write_obs(p.terminal_obs, n, env, j, q, a.rep, des_j, ach_j, a.tol, sysid, a.obs_dim);
+                write_obs(p.terminal_obs, n, env, j, bf, af, bprev, aprev, a.rep, des_j, ach_j, a.tol, sysid, a.obs_dim);
                 p.terminal_achieved[(int64_t)j * n + env] = ach_j;
             }
             if (j == 0) {
@@ -963,6 +978,10 @@ KArgs make_args(const ctr_handle* h) {
 inline int grid_for(int64_t n_envs) { return (int)((n_envs + ENVS_PER_BLOCK - 1) / ENVS_PER_BLOCK); }
 
 // k_step additionally specialises on "every tube has y_curvature == 0" (template INTEG bit 1, see rhs)
+#ifdef CTR_DEV_ONLY_D2   // development build: only the headline instantiations are compiled (ptxas -v / SASS turnaround)
+#define DISPATCH_STEP(uy0, integ, prec, ...) do { k_step<double, 2> __VA_ARGS__; } while (0)
+#define DISPATCH(KERNEL, integ, prec, ...) do { KERNEL<double, 0> __VA_ARGS__; } while (0)
+#else
 #define DISPATCH_STEP(uy0, integ, prec, ...)                                         \
     do {                                                                             \
         const int sel__ = ((integ) == CTR_INTEGRATOR_DP45 ? 0 : 1) | ((uy0) ? 2 : 0); \
@@ -989,6 +1008,7 @@ inline int grid_for(int64_t n_envs) { return (int)((n_envs + ENVS_PER_BLOCK - 1)
             else KERNEL<float, 1> __VA_ARGS__;                                       \
         }                                                                            \
     } while (0)
+#endif
 
 int launch_reset(ctr_handle* h, const int32_t* list, const int32_t* count_ptr, int64_t max_items, const double* goal,
                  const int32_t* system, cudaStream_t st) {
