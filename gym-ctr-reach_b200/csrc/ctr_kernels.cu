@@ -52,6 +52,12 @@ constexpr int BLOCK = CTR_BLOCK;                 // 4 warps = 40 environments pe
 #endif
 constexpr int MIN_BLOCKS = CTR_MIN_BLOCKS;       // 16 warps / SM: register cap 65536 / 512 = 128 (measured: 12 and 20 warps / SM are slower)
 constexpr int ENVS_PER_BLOCK = (BLOCK / 32) * ENVS_PER_WARP;
+// register limit of the FK kernels: by resident blocks (default) or, for occupancy experiments, as an explicit count
+#ifdef CTR_MAXNREG
+#define CTR_FK_BOUNDS __maxnreg__(CTR_MAXNREG)
+#else
+#define CTR_FK_BOUNDS __launch_bounds__(BLOCK, MIN_BLOCKS)
+#endif
 #ifndef CTR_SORT_WINDOW
 #define CTR_SORT_WINDOW 640
 #endif
@@ -203,7 +209,7 @@ __device__ __forceinline__ void write_obs(double* obs, int64_t n, int64_t env, i
 
 // ------------------------------------------------------------------------------------------------------------
 template <typename T, int INTEG>
-__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk(const SysConst* __restrict__ sys, int n_systems,
+__global__ void CTR_FK_BOUNDS k_fk(const SysConst* __restrict__ sys, int n_systems,
                                               const double* __restrict__ joints, const int32_t* __restrict__ system,
                                               const double* __restrict__ params, int64_t n, double rtol, double atol,
                                               int rk4_steps, double* __restrict__ tip, double* __restrict__ R,
@@ -251,7 +257,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk(const SysConst* __rest
 // L_k + beta_k - 1e-3 (the split points of r1 / r2 / r3).  shape f64 [n][max_pts][3], npts i32 [n], tip_idx i32 [3][n].
 // UY0: every system has y_curvature == 0 and no per-env parameters are given (the instantiation k_step uses, see rhs()).
 template <bool UY0>
-__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_fk_shape(const SysConst* __restrict__ sys, int n_systems,
+__global__ void CTR_FK_BOUNDS k_fk_shape(const SysConst* __restrict__ sys, int n_systems,
                                                     const double* __restrict__ joints, const int32_t* __restrict__ system,
                                                     const double* __restrict__ params, int64_t n, double rtol, double atol,
                                                     int max_pts, double* __restrict__ shape, int32_t* __restrict__ npts,
@@ -325,7 +331,7 @@ __device__ __forceinline__ void reset_envs(const KArgs& a, const LaneId& id, con
 // runs out of step work).  A slot that is not ready (tag != episode + 1: first step of an episode, after seed()/
 // explicit resets) falls back to the in-place reset by the env's own warp; both paths give identical bits.
 template <typename T, int INTEG>
-__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_step(const KArgs a, const float* __restrict__ action) {
+__global__ void CTR_FK_BOUNDS k_step(const KArgs a, const float* __restrict__ action) {
     __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
     __shared__ GroupScratch s_gs[(BLOCK / 32) * SLOTS_PER_WARP];
     stage_sys(s_sys, a.sys, a.n_systems);
@@ -759,7 +765,7 @@ __device__ __forceinline__ void reset_envs(const KArgs& a, const LaneId& id, con
 }
 
 template <typename T, int INTEG>
-__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) k_reset(const KArgs a, const int32_t* __restrict__ list,
+__global__ void CTR_FK_BOUNDS k_reset(const KArgs a, const int32_t* __restrict__ list,
                                                  const int32_t* __restrict__ count_ptr, const double* __restrict__ goal,
                                                  const int32_t* __restrict__ system_in) {
     __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
