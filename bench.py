@@ -80,23 +80,46 @@ def host_cores():
 
 
 # ------------------------------------------------------------------------------------------------ CPU baseline
-def _cpu_worker(rank, n_envs, warmup, steps, barrier, out_q, integrator):
-    """The oracle port of the reference step (test infrastructure used here as the timed CPU baseline)."""
+def ref_available():
+    """The unmodified reference step path: /root/reference in the build container, oracle/_ref/ (staged by oracle/make_ref.py,
+    travels with the snapshot) on the GPU box."""
+    return any(os.path.isfile(os.path.join(r, 'ctr_reach_envs', 'envs', 'model.py'))
+               for r in ('/root/reference', os.path.join(ROOT, 'oracle', '_ref')))
+
+
+def _cpu_worker(rank, n_envs, warmup, steps, barrier, out_q, kind):
+    """One process pinned to one core stepping n_envs single envs: kind 'reference' = the reference's own CtrReachEnv
+    (gym.make('CTR-Reach-v0') through oracle/ref_loader.py, its own scipy RK45 path), 'port' = the oracle port of the same step
+    (test infrastructure used here as a timed CPU baseline)."""
     try:
         os.sched_setaffinity(0, {sorted(os.sched_getaffinity(0))[rank % len(os.sched_getaffinity(0))]})
     except Exception:
         pass
     os.environ.setdefault('OMP_NUM_THREADS', '1')
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
-    import ctr_oracle as O
-    envs = [O.OracleEnv(seed=1000 * rank + i, integrator=integrator) for i in range(n_envs)]
+    import numpy as np
+    np.random.seed(1000 + rank)
+    if kind == 'reference':
+        import ref_loader
+        _, gym = ref_loader.load()
+        gym.spaces.seed(7919 * rank + 1)                         # the stand-in Box spaces draw from one module-level RNG
+        envs = [gym.make('CTR-Reach-v0') for _ in range(n_envs)]
+
+        def step_env(e):
+            _, _, done, _ = e.step(e.action_space.sample())     # done already includes t >= 150 (ctr_reach_env.py:140)
+            return done
+    else:
+        import ctr_oracle as O
+        envs = [O.OracleEnv(seed=1000 * rank + i, integrator='scipy') for i in range(n_envs)]
+
+        def step_env(e):
+            return e.step(e.sample_action())[2]
     for e in envs:
         e.reset()
 
     def one_step():
         for e in envs:
-            _, _, done, _ = e.step(e.sample_action())
-            if done:
+            if step_env(e):
                 e.reset()
 
     for _ in range(warmup):
@@ -110,13 +133,13 @@ def _cpu_worker(rank, n_envs, warmup, steps, barrier, out_q, integrator):
     out_q.put((rank, t0, t1))
 
 
-def run_cpu_port(steps, warmup, envs_per_core=4, cores=None, integrator='scipy'):
-    """P processes x envs_per_core oracle envs; returns (env-steps/s aggregate, seconds per step, cores)."""
+def run_cpu(kind, steps, warmup, envs_per_core, cores=None):
+    """P processes x envs_per_core single envs; returns (env-steps/s aggregate, seconds per step, cores)."""
     cores = cores or host_cores()
     ctx = mp.get_context('spawn')   # the parent may hold a CUDA context: never fork it
     barrier = ctx.Barrier(cores)
     q = ctx.Queue()
-    procs = [ctx.Process(target=_cpu_worker, args=(r, envs_per_core, warmup, steps, barrier, q, integrator)) for r in range(cores)]
+    procs = [ctx.Process(target=_cpu_worker, args=(r, envs_per_core, warmup, steps, barrier, q, kind)) for r in range(cores)]
     for p in procs:
         p.start()
     res = [q.get() for _ in range(cores)]
@@ -153,22 +176,32 @@ def run_cpu_c_port(seconds=4.0):
     return done_steps / (time.perf_counter() - t0), cores
 
 
+REF_ENVS_PER_CORE = 48      # one reference-arm "step" = every process steps its 48 envs once (0.3 s at the 167 steps/s/core of the GPU box's host, 1 s at 47)
+
+
 def reference_arm(args):
+    """The reference's own CPU implementation of the path on all host cores: the unmodified CtrReachEnv when its files are
+    present (kind "reference"), else the oracle port (kind "port", said so in the line)."""
     rank = int(os.environ.get('RANK', 0))
     if rank != 0:
         return 0
     cores = host_cores()
-    envs_per_core = 4
-    value, sec_per_step, cores = run_cpu_port(args.steps, max(args.warmup, 1), envs_per_core, cores)
-    sample = "%d processes x %d envs, %d timed steps each (system 0, tol 0.02, sparse reward, random actions, reset on done)" % (
-        cores, envs_per_core, args.steps)
+    kind = 'reference' if ref_available() else 'port'
+    value, sec_per_step, cores = run_cpu(kind, args.steps, max(args.warmup, 1), REF_ENVS_PER_CORE, cores)
+    sample = "%d processes x %d envs, %d timed steps each = %.1f s (system 0, tol 0.02, sparse reward, random actions, reset on done)" % (
+        cores, REF_ENVS_PER_CORE, args.steps, sec_per_step * args.steps)
+    note = ("the UNMODIFIED reference: gym.make('CTR-Reach-v0') -> CtrReachEnv.step (python ode_eq + scipy solve_ivp RK45), files "
+            "staged by oracle/make_ref.py, gym / matplotlib stand-ins + the numpy>=1.24 load-time patch of model.py:107"
+            if kind == 'reference' else
+            "oracle/_ref absent: oracle PORT of the reference step (python ode_eq + scipy.integrate.solve_ivp(RK45)); about 2.9x "
+            "faster per core than the reference itself")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": sec_per_step * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(args), "cpu_batch": cores * envs_per_core},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
-                         "note": "oracle port of the reference step: python ode_eq + scipy.integrate.solve_ivp(RK45), one process per core"},
+        "config": {"workload": workload_name(args), "cpu_batch": cores * REF_ENVS_PER_CORE},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
+                         "per_core": value / cores, "note": note},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -211,7 +244,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._halt.wait(0.02)
+            self._halt.wait(0.002)
 
     def stop(self):
         self._halt.set()
@@ -247,6 +280,11 @@ def gpu_arm(args):
                                      precision=args.precision, rk4_steps=args.rk4_steps, reward_mode='sparse', seed=0)
     env.goal_tolerance.current_tol = args.tol
     env.reset()
+    # steady state, not a synchronised start: episode phases are spread over the 150-step time limit (t = global env index
+    # mod 150), so the timed window carries the time-limit resets of a long-running job (>= 1/150 of the envs per step on top
+    # of the early successes) and no refill wave; the warm-up below lets the prefetch queues reach their steady load
+    lo = rank * N
+    env.set_state(t=((lo + np.arange(N)) % env.max_steps_per_episode).astype(np.int32))
 
     # synthetic actions resident in HBM: a pool of distinct uniform draws in the action box, (N, 6) row-major
     lim = torch.tensor(env.action_space.high, device=dev)
@@ -260,7 +298,8 @@ def gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    for i in range(max(args.warmup, 3)):
+    n_warm = max(args.warmup, 10)
+    for i in range(n_warm):
         env.step(pool[i % len(pool)])
     barrier()
     env.stats_reset()
@@ -344,17 +383,19 @@ def gpu_arm(args):
         hbm_peak, hbm_src = 6650.0, "fallback"
         if os.path.exists(peaks_file):
             hbm_peak, hbm_src = json.load(open(peaks_file))['hbm_gbs'], "measured (MEASURED_PEAKS.json)"
-        traffic = None
+        traffic, traffic_src = None, None
         tfile = os.path.join(ROOT, 'profiles', 'traffic.json')
         if os.path.exists(tfile):
-            traffic = json.load(open(tfile)).get('k_step_dram_bytes_per_launch')
+            tj = json.load(open(tfile))
+            traffic, traffic_src = tj.get('k_step_dram_bytes_per_launch'), "ncu capture of kernel commit %s (%s)" % (tj.get('kernel_commit'), tj.get('source', '')[:60])
         hbm_achieved = BYTES_PER_STEP * N / (k_ms * 1e-3) / 1e9
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": n_warm,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": args.precision, "data": "synthetic",
             "config": {"workload": workload_name(args), "total_envs": total, "integrator": args.integrator,
                        "l2": "flushed between timed steps (256 MiB memset outside the event pairs)",
+                       "episode_phase": "t = global env index mod 150 before warm-up (steady-state reset load, no synchronised refill wave)",
                        "timing": "one CUDA event pair per step on the launch stream, summed; max over ranks"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
                     "host_cpus_rank0": (("%d cpus local to the GPU (NVML affinity)" % len(numa_cpus)) if numa_cpus else "unbound"),
@@ -362,7 +403,7 @@ def gpu_arm(args):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "fma", "kernel": "k_step<%s,%s>" % (args.precision, args.integrator), "achieved": achieved,
-                         "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic,
+                         "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": "measured live: register-resident %s FMA chains (ctr_measure_fma_peak); "
                                         "MEASURED_PEAKS.json has no FP64/FP32 FMA figure" % args.precision,
                          "flop_per_launch": flop_per_launch, "kernel_ms": k_ms,
@@ -375,11 +416,18 @@ def gpu_arm(args):
         }
         if world == 1 and not args.no_cpu:
             t_c = time.perf_counter()
-            v, _, cores = run_cpu_port(args.cpu_steps, 1, envs_per_core=2)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                                    "sample": "%d processes x 2 envs x %d steps of the same workload (python + scipy RK45 port of the reference step), %.1f s"
-                                              % (cores, args.cpu_steps, time.perf_counter() - t_c)}
+            kind = 'reference' if ref_available() else 'port'
+            v, _, cores = run_cpu(kind, args.cpu_steps, 2, envs_per_core=8)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "per_core": v / cores,
+                                    "sample": "%d processes x 8 envs x %d steps of the same workload (%s), %.1f s"
+                                              % (cores, args.cpu_steps,
+                                                 "unmodified reference CtrReachEnv from oracle/_ref" if kind == 'reference'
+                                                 else "oracle port: oracle/_ref absent", time.perf_counter() - t_c)}
             try:
+                t_c = time.perf_counter()
+                vp, _, cp = run_cpu('port', 4 * args.cpu_steps, 2, envs_per_core=4)
+                line["cpu_baseline"]["py_port"] = {"value": vp, "unit": UNIT, "cores": cp, "seconds": time.perf_counter() - t_c,
+                                                   "note": "oracle/ctr_oracle.py OracleEnv: same python ode_eq + scipy RK45, scalar trig"}
                 vc, cc = run_cpu_c_port(3.0)
                 line["cpu_baseline"]["c_port"] = {"value": vc, "unit": UNIT, "cores": cc, "note": "plain-C restatement (oracle/ctr_oracle.c), pthreads"}
             except Exception as exc:  # pragma: no cover
@@ -387,8 +435,10 @@ def gpu_arm(args):
             line["tip_error_m"] = tip_error_check(env)
         if world == 1 and not args.no_kernel_table:
             line["kernels"] = kernel_table(args, dev, pool, peak, hbm_peak)
-        if world == 1 and args.extras:
-            line["extra"] = extras(args, dev, pool)
+        if world == 1 and not args.no_extra:
+            line["extra"] = extras_default(args, dev, pool)
+            if args.extras:
+                line["extra"].update(extras(args, dev, pool))
     env.close()
     if line is not None:
         emit(line)
@@ -535,6 +585,82 @@ def kernel_table(args, dev, pool, fma_peak, hbm_peak):
     return tab
 
 
+def _time_env(args, dev, pool, n, steps, tol=None, curriculum=None, **kw):
+    """env-steps/s of a CtrReachVecEnv variant: back-to-back steps after 5 warm-up steps, one CUDA event pair."""
+    import torch
+    import ctr_reach_envs
+    from ctr_reach_envs.envs import CtrReachVecEnv
+    k = ctr_reach_envs.default_kwargs()
+    k.update(kw)
+    if curriculum:            # decay schedule of saved_policies/**/env_parameters.yml (SURVEY 8d cfg 5), advanced every step
+        k['goal_tolerance_parameters'] = dict(k['goal_tolerance_parameters'], **curriculum)
+    e = CtrReachVecEnv(n, device=dev.index, **k)
+    if not curriculum:
+        e.goal_tolerance.current_tol = args.tol if tol is None else tol
+    e.reset()
+    acts = [p[:n].contiguous() if p.shape[0] >= n else p.repeat((n + p.shape[0] - 1) // p.shape[0], 1)[:n].contiguous() for p in pool[:4]]
+    for i in range(5):
+        e.step(acts[i % 4])
+    torch.cuda.synchronize(dev)
+    s, t = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for i in range(steps):
+        if curriculum:
+            e.update_goal_tolerance(1000 * i)           # host-side scalar schedule -> ctr_set_tolerance
+        e.step(acts[i % 4])
+    t.record()
+    torch.cuda.synchronize(dev)
+    e.close()
+    return n * steps / (s.elapsed_time(t) * 1e-3)
+
+
+CURRICULUM = {'function': 'decay', 'initial_tol': 0.020, 'final_tol': 0.001, 'N_ts': 1.5e6, 'set_tol': 0}
+
+
+def extras_default(args, dev, pool):
+    """Always part of the 1-GPU line: a 450-step run from a synchronised start (what the headline window does not show: the
+    refill wave after t = 150), BASELINE.json config 2 and config 5."""
+    import numpy as np
+    import torch
+    import ctr_reach_envs
+    from ctr_reach_envs.envs import CtrReachVecEnv
+    res = {}
+    N = args.envs_per_gpu
+    e = CtrReachVecEnv(N, device=dev.index, **ctr_reach_envs.default_kwargs())
+    e.goal_tolerance.current_tol = args.tol
+    e.reset()
+    steps = 450
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    e.stats_reset()
+    resets = []
+    ev[0].record()
+    for i in range(steps):
+        e.step(pool[i % len(pool)])
+        ev[i + 1].record()
+        if i in (149, 299, 449):
+            resets.append(e.stats(reduce=False)['resets'])
+    torch.cuda.synchronize(dev)
+    ms = np.array([ev[i].elapsed_time(ev[i + 1]) for i in range(steps)])
+    st = e.stats(reduce=False)
+    e.close()
+    tail = ms[300:]
+    res["long_run"] = {
+        "steps": steps, "start": "synchronised (every env at t = 0), back-to-back steps, no L2 flush",
+        "ms_per_step_mean": float(ms.mean()), "ms_per_step_p50": float(np.percentile(ms, 50)),
+        "ms_per_step_p99": float(np.percentile(ms, 99)), "ms_per_step_max": float(ms.max()), "argmax_step": int(ms.argmax()),
+        "ms_per_step_mean_steps_300_449": float(tail.mean()),
+        "env_steps_per_s_steps_300_449": N / (tail.mean() * 1e-3),
+        "reset_fraction": st['resets'] / max(st['env_steps'], 1.0),
+        "reset_fraction_by_150_steps": [float(b - a) / (150.0 * N) for a, b in zip([0.0] + resets[:-1], resets)],
+        "success_rate": st['success_rate'], "mean_episode_length": st['mean_episode_length']}
+    res["cfg2_4096_envs_dense_reward"] = {"value": _time_env(args, dev, pool, 4096, 300, reward_mode='dense'), "unit": UNIT,
+                                          "note": "4096 envs are 103 blocks on 148 SMs: latency of one FK wave, back-to-back steps"}
+    res["cfg5_domain_rand_tolerance_curriculum_131072_envs"] = {
+        "value": _time_env(args, dev, pool, ENVS_PER_GPU, 30, domain_rand=0.05, curriculum=CURRICULUM), "unit": UNIT,
+        "note": "per-env tube parameters (stiffness, curvature, diameters) +-5 % at every reset; tolerance 0.02 -> 0.001 decay advanced every step"}
+    return res
+
+
 def extras(args, dev, pool):
     """Other BASELINE.json configs on one GPU (reported beside the headline, not the headline)."""
     import torch
@@ -543,39 +669,13 @@ def extras(args, dev, pool):
     res = {}
 
     def time_env(n, steps, tol=None, curriculum=None, **kw):
-        k = ctr_reach_envs.default_kwargs()
-        k.update(kw)
-        if curriculum:            # decay schedule of saved_policies/**/env_parameters.yml (SURVEY 8d cfg 5), advanced every step
-            k['goal_tolerance_parameters'] = dict(k['goal_tolerance_parameters'], **curriculum)
-        e = CtrReachVecEnv(n, device=dev.index, **k)
-        if not curriculum:
-            e.goal_tolerance.current_tol = args.tol if tol is None else tol
-        e.reset()
-        acts = [p[:n].contiguous() if p.shape[0] >= n else p.repeat((n + p.shape[0] - 1) // p.shape[0], 1)[:n].contiguous() for p in pool[:4]]
-        for i in range(5):
-            e.step(acts[i % 4])
-        torch.cuda.synchronize(dev)
-        s, t = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        for i in range(steps):
-            if curriculum:
-                e.update_goal_tolerance(1000 * i)           # host-side scalar schedule -> ctr_set_tolerance
-            e.step(acts[i % 4])
-        t.record()
-        torch.cuda.synchronize(dev)
-        e.close()
-        return n * steps / (s.elapsed_time(t) * 1e-3)
+        return _time_env(args, dev, pool, n, steps, tol=tol, curriculum=curriculum, **kw)
 
-    res["cfg2_4096_envs_dense_reward"] = {"value": time_env(4096, 300, reward_mode='dense'), "unit": UNIT, "note": "back-to-back steps, no L2 flush"}
     res["cfg3_2^20_envs_one_gpu"] = {"value": time_env(1 << 20, 10), "unit": UNIT}
     for integ, prec in (('dp45', 'f32'), ('rk4', 'f64'), ('rk4', 'f32')):
         res["%s_%s_131072_envs" % (integ, prec)] = {"value": time_env(ENVS_PER_GPU, 30, integrator=integ, precision=prec), "unit": UNIT,
                                                      "note": "does NOT meet the 1e-5 m bar on all configs (see DESIGN.md)"}
     res["cfg5_domain_rand_131072_envs"] = {"value": time_env(ENVS_PER_GPU, 30, domain_rand=0.05), "unit": UNIT}
-    res["cfg5_domain_rand_tolerance_curriculum_131072_envs"] = {
-        "value": time_env(ENVS_PER_GPU, 30, domain_rand=0.05,
-                          curriculum={'function': 'decay', 'initial_tol': 0.020, 'final_tol': 0.001, 'N_ts': 1.5e6, 'set_tol': 0}),
-        "unit": UNIT, "note": "per-env tube parameters +-5 % at every reset; tolerance 0.02 -> 0.001 decay advanced every step"}
     res["cfg3_tol_0.001_131072_envs"] = {"value": time_env(ENVS_PER_GPU, 30, tol=0.001), "unit": UNIT,
                                           "note": "almost nobody succeeds: episodes end at 150 steps, lowest reset load"}
     # cfg 4: HER compute_reward + relabel on 2^20 transitions (HBM bound: 80 B / transition)
@@ -672,10 +772,11 @@ def main():
     ap.add_argument('--integrator', default='dp45', choices=['dp45', 'rk4'])
     ap.add_argument('--precision', default='f64', choices=['f64', 'f32'])
     ap.add_argument('--rk4-steps', type=int, default=8)
-    ap.add_argument('--cpu-steps', type=int, default=2500, help='timed steps of the CPU port per process (2 envs each): ~15 s on 16 cores')
+    ap.add_argument('--cpu-steps', type=int, default=200, help='timed steps of the CPU reference per process (8 envs each): ~10 s at 167 steps/s/core')
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--no-kernel-table', action='store_true', help='skip the per-kernel roofline table (1 GPU)')
-    ap.add_argument('--extras', action='store_true', help='also time the other BASELINE.json configs (1 GPU)')
+    ap.add_argument('--extras', action='store_true', help='also time the remaining BASELINE.json configs and variants (1 GPU)')
+    ap.add_argument('--no-extra', action='store_true', help='skip the default extra block (long run, cfg 2, cfg 5)')
     args = ap.parse_args()
     claim_stdout()
     if args.impl == 'reference':

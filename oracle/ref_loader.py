@@ -15,8 +15,20 @@ import importlib.machinery
 import os
 import sys
 
-REF_ROOT = os.environ.get('CTR_REFERENCE_ROOT', '/root/reference')
-_SHIM = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'ref_shim')
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SHIM = os.path.join(_HERE, 'ref_shim')
+
+
+def _default_root():
+    # the build container has the reference itself; the GPU box only has the byte-for-byte copies of the step-path files
+    # that oracle/make_ref.py staged under oracle/_ref/ (git-ignored, travels with the snapshot)
+    for root in ('/root/reference', os.path.join(_HERE, '_ref')):
+        if os.path.isfile(os.path.join(root, 'ctr_reach_envs', 'envs', 'model.py')):
+            return root
+    return '/root/reference'
+
+
+REF_ROOT = os.environ.get('CTR_REFERENCE_ROOT') or _default_root()
 
 
 class _PatchedLoader(importlib.machinery.SourceFileLoader):
