@@ -658,6 +658,9 @@ def extras_default(args, dev, pool):
     res["cfg5_domain_rand_tolerance_curriculum_131072_envs"] = {
         "value": _time_env(args, dev, pool, ENVS_PER_GPU, 30, domain_rand=0.05, curriculum=CURRICULUM), "unit": UNIT,
         "note": "per-env tube parameters (stiffness, curvature, diameters) +-5 % at every reset; tolerance 0.02 -> 0.001 decay advanced every step"}
+    res["cfg5_with_length_randomisation_131072_envs"] = {
+        "value": _time_env(args, dev, pool, ENVS_PER_GPU, 30, domain_rand=0.05, domain_rand_length=0.05, curriculum=CURRICULUM), "unit": UNIT,
+        "note": "as above plus tube lengths +-5 % with per-env joint limits (extension: the reference forbids it, model_utils.py:12-14)"}
     return res
 
 

@@ -31,7 +31,6 @@ struct SysConst {
     float low[6], high[6];                           // joint Box bounds, float32 (obs.py:59-75)
     float d10, d21;                                  // f32(L1 - L0), f32(L2 - L1) (obs.py:181, NEP-50 weak python float)
     float Lf[3];                                     // f32(L_i) for the goal-sampling predicate (obs.py:198-200)
-    float slow[3];                                   // sample-space low for beta (obs.py:59-63)
 };
 
 struct LaneId {
@@ -853,15 +852,49 @@ __device__ __forceinline__ void fk_group_shape(const LaneId& id, bool valid, Gro
     __syncwarp();
 }
 
+// ---- joint limits of one environment (obs.py:24-29,50-76) ------------------------------------------------------------
+// The reference derives them from the tube lengths of the SYSTEM; with per-env tube lengths (ctr_set_tube_params, or
+// domain_rand_length > 0 -- an extension, the reference forbids length randomisation, model_utils.py:12-14) they follow the
+// env's own lengths with the same float32 roundings: low_i = f32(-L_i + 1e-3), d10 = f32(L_1 - L_0), d21 = f32(L_2 - L_1).
+struct JointLimits {
+    float low[6], high[6];   // Box bounds (beta: [-L + 1e-3, 0]; alpha: +-pi or +-inf)
+    float d10, d21;          // ordering constants of obs.py:181
+    float Lf[3];             // f32(L_i): goal-sampling predicate (obs.py:198-200)
+};
+__device__ __forceinline__ void limits_of_system(const SysConst& sc, JointLimits& lim) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        lim.low[i] = sc.low[i];
+        lim.high[i] = sc.high[i];
+    }
+    lim.d10 = sc.d10;
+    lim.d21 = sc.d21;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) lim.Lf[i] = sc.Lf[i];
+}
+// L: this env's tube lengths (float64).  For L equal to the system's lengths the result is bit-identical to limits_of_system.
+__device__ __forceinline__ void limits_of_lengths(const SysConst& sc, const double* L, JointLimits& lim) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        lim.low[i] = (float)__dadd_rn(-L[i], 1e-3);
+        lim.high[i] = 0.f;
+        lim.low[3 + i] = sc.low[3 + i];
+        lim.high[3 + i] = sc.high[3 + i];
+        lim.Lf[i] = (float)L[i];
+    }
+    lim.d10 = (float)__dsub_rn(L[1], L[0]);
+    lim.d21 = (float)__dsub_rn(L[2], L[1]);
+}
+
 // ---- Obs.set_action x n_substeps (obs.py:166-183, ctr_reach_env.py:134-135), float32 arithmetic -------------
-__device__ __forceinline__ void set_action(float (&q)[6], const float (&a)[6], const SysConst& sc, int n_substeps) {
+__device__ __forceinline__ void set_action(float (&q)[6], const float (&a)[6], const JointLimits& lim, int n_substeps) {
     for (int s = 0; s < n_substeps; ++s) {
 #pragma unroll
-        for (int i = 0; i < 6; ++i) q[i] = fminf(fmaxf(__fadd_rn(q[i], a[i]), sc.low[i]), sc.high[i]);   // obs.py:172
+        for (int i = 0; i < 6; ++i) q[i] = fminf(fmaxf(__fadd_rn(q[i], a[i]), lim.low[i]), lim.high[i]);   // obs.py:172
         q[0] = fminf(q[0], q[1]);                                   // obs.py:180 (i = 1)
-        q[0] = fmaxf(q[0], __fadd_rn(sc.d10, q[1]));                // obs.py:181
+        q[0] = fmaxf(q[0], __fadd_rn(lim.d10, q[1]));               // obs.py:181
         q[1] = fminf(q[1], q[2]);                                   // i = 2
-        q[1] = fmaxf(q[1], __fadd_rn(sc.d21, q[2]));
+        q[1] = fmaxf(q[1], __fadd_rn(lim.d21, q[2]));
     }
 }
 
@@ -882,7 +915,7 @@ __device__ __forceinline__ double u01(unsigned x) { return (double)x * (1.0 / 42
 
 // Obs.sample_goal (obs.py:185-207): uniform float32 box beta in [-L+1e-3, 0], alpha in [-pi, pi]; accept iff
 // b0 <= b1 <= b2 and b_{i-1} + L_{i-1} >= L_i + b_i (float32 arithmetic).  Returns the number of draws.
-__device__ __forceinline__ int sample_goal(const SysConst& sc, uint2 key, unsigned env_lo, unsigned env_hi,
+__device__ __forceinline__ int sample_goal(const JointLimits& sc, uint2 key, unsigned env_lo, unsigned env_hi,
                                            unsigned episode, unsigned stream, float (&q)[6], bool& ok) {
     int tries = 0;
     ok = false;
@@ -892,7 +925,7 @@ __device__ __forceinline__ int sample_goal(const SysConst& sc, uint2 key, unsign
         unsigned rr[3] = {r.x, r.y, r.z};
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
-            double lo = (double)sc.slow[i];
+            double lo = (double)sc.low[i];             // sample-space low of beta = the Box low (obs.py:59-63)
             q[i] = (float)(lo + (0.0 - lo) * u01(rr[i]));   // uniform(low, high).astype(float32)
         }
         tries += 1;

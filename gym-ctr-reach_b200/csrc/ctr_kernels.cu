@@ -67,7 +67,7 @@ constexpr int ENVS_PER_BLOCK = (BLOCK / 32) * ENVS_PER_WARP;
 constexpr int SORT_WINDOW = CTR_SORT_WINDOW;                 // slots per sorting window (16 blocks); launches start on window boundaries
 constexpr int N_STATS = 16;
 enum { ST_EPISODES = 0, ST_SUCCESSES, ST_SUM_ERROR, ST_SUM_RETURN, ST_SUM_LENGTH, ST_STEPS, ST_RESETS, ST_DRAWS,
-       ST_FK_FAILED, ST_GOAL_STUCK, ST_NFEV, ST_ATTEMPTS, ST_SECTIONS, ST_FK_COUNT };
+       ST_FK_FAILED, ST_GOAL_STUCK, ST_NFEV, ST_ATTEMPTS, ST_SECTIONS, ST_FK_COUNT, ST_INVALID_ACTION };
 
 struct DevPtrs {
     float* joints;
@@ -115,6 +115,10 @@ struct KArgs {
     int32_t n_systems, n_substeps, max_steps, rep, reward_mode, auto_reset, resample_joints, rk4_steps, obs_dim;
     int32_t use_params;        // tube_params holds valid per-env constants
     double tol, rtol, atol, domain_rand;
+    double domain_rand_length; // +-fraction on L and L_c at every reset (extension, 0 = reference behaviour)
+    float act_lim_ext, act_lim_rot;   // action Box half-widths as float32 (ctr_reach_env.py:55-62)
+    int32_t action_scale;      // actions arrive in [-1, 1] and are multiplied by the limits (extension)
+    int32_t action_clip;       // out-of-box components are clipped, NaN components zeroed (default: passed through, counted)
     uint2 key;
     int64_t env_offset;
     int64_t act_stride_field, act_stride_env;   // action element (i, env) at action[i * stride_field + env * stride_env]
@@ -360,12 +364,31 @@ __global__ void CTR_FK_BOUNDS k_step(const KArgs a, const float* __restrict__ ac
         const int sysid = p.system[e];
         const SysConst& sc = s_sys[sysid];
         float q[6], act[6];
+        bool bad_action = false;       // ctr_reach_env.py:131-132: the reference asserts; a batch cannot raise per env, it counts
 #pragma unroll
         for (int i = 0; i < 6; ++i) {
             q[i] = p.joints[(int64_t)i * n + e];
-            act[i] = action[(int64_t)i * a.act_stride_field + e * a.act_stride_env];
+            float v = action[(int64_t)i * a.act_stride_field + e * a.act_stride_env];
+            const float lim_i = (i < 3) ? a.act_lim_ext : a.act_lim_rot;
+            if (a.action_scale) {                                              // normalised policy output -> joint deltas
+                bad_action |= !(fabsf(v) <= 1.0f);
+                v = __fmul_rn(fminf(fmaxf(v, -1.0f), 1.0f), lim_i);            // NaN -> -lim (fmaxf drops the NaN); counted above
+            } else {
+                bad_action |= !(fabsf(v) <= lim_i);                            // action_space.contains(): NaN or outside the Box
+            }
+            if (a.action_clip) v = (v == v) ? fminf(fmaxf(v, -lim_i), lim_i) : 0.0f;
+            act[i] = v;
         }
-        set_action(q, act, sc, a.n_substeps);                                  // ctr_reach_env.py:134-135
+        JointLimits lim;
+        if (a.use_params) {            // per-env tube lengths carry per-env joint limits
+            double Le[3];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) Le[i] = __ldg(p.tube_params + (int64_t)i * n + e);
+            limits_of_lengths(sc, Le, lim);
+        } else {
+            limits_of_system(sc, lim);
+        }
+        set_action(q, act, lim, a.n_substeps);                                 // ctr_reach_env.py:134-135
         // the new joints are final here: store them now and fetch the lane's own pair back after the solve, so that no
         // joint value occupies a register across the integration loop (it runs at the 128-register limit)
         if (valid) {
@@ -395,7 +418,7 @@ __global__ void CTR_FK_BOUNDS k_step(const KArgs a, const float* __restrict__ ac
         const double s0 = __shfl_sync(FULL, sq, id.l0), s1 = __shfl_sync(FULL, sq, id.l0 + 1), s2 = __shfl_sync(FULL, sq, id.l0 + 2);
         const double dist = __dsqrt_rn(__dadd_rn(__dadd_rn(s0, s1), s2));
         const int t_new = p.t[e] + 1;
-        const bool far = dist > a.tol;
+        const bool far = !(dist <= a.tol);     // dist > tol (ctr_reach_env.py:169); a NaN distance (failed solve) is far, not done
         const double reward = (a.reward_mode == CTR_REWARD_DENSE) ? -dist : (far ? -1.0 : -0.0);
         const bool done = (!far) || (t_new >= a.max_steps);
         const bool success = dist < a.tol;
@@ -547,6 +570,7 @@ __global__ void CTR_FK_BOUNDS k_step(const KArgs a, const float* __restrict__ ac
         double v_ln = (lead && done) ? (double)t_new : 0.0;
         double v_st = lead ? 1.0 : 0.0;
         double v_fl = (lead && info.failed) ? 1.0 : 0.0;
+        const unsigned bad_mask = __ballot_sync(FULL, lead && bad_action);
         double v_nf = lead ? (double)info.nfev : 0.0;
         double v_at = lead ? (double)(info.nacc + info.nrej) : 0.0;
         double v_sc = lead ? (double)info.nsec : 0.0;
@@ -567,6 +591,7 @@ __global__ void CTR_FK_BOUNDS k_step(const KArgs a, const float* __restrict__ ac
             atomicAdd(p.stats + ST_SECTIONS, v_sc);
             atomicAdd(p.stats + ST_FK_COUNT, v_st);
             if (v_fl != 0.0) atomicAdd(p.stats + ST_FK_FAILED, v_fl);
+            if (bad_mask) atomicAdd(p.stats + ST_INVALID_ACTION, (double)__popc(bad_mask));
         }
     }
     // ---- reset work of this warp, 5 environments at a time (group pairs, see reset_envs): first the in-place resets
@@ -644,8 +669,12 @@ __device__ __forceinline__ void reset_envs(const KArgs& a, const LaneId& id, con
             double E = rnd(nom[tb * 8 + 4], r1.z), Gm = rnd(nom[tb * 8 + 5], r1.w), ux = rnd(nom[tb * 8 + 6], r2.x);
             double do2 = d_o * d_o, di2 = di * di;
             double d4 = do2 * do2 - di2 * di2;
-            C[tb] = nom[tb * 8 + 0];
-            C[3 + tb] = nom[tb * 8 + 1];
+            // lengths: untouched in the reference (model_utils.py:12-14); domain_rand_length > 0 is the extension
+            // BASELINE.json config 5 names -- the same U(v - v r, v + v r) on L and L_c, joint limits follow (JointLimits)
+            const double rl = a.domain_rand_length;
+            auto rndl = [rl](double v, unsigned bits) { return (v - v * rl) + ((v + v * rl) - (v - v * rl)) * u01(bits); };
+            C[tb] = (rl > 0.0) ? rndl(nom[tb * 8 + 0], r2.y) : nom[tb * 8 + 0];
+            C[3 + tb] = (rl > 0.0) ? rndl(nom[tb * 8 + 1], r2.z) : nom[tb * 8 + 1];
             C[6 + tb] = E * ((3.141592653589793 * d4) / 64);           // Tube.py:15
             C[9 + tb] = Gm * ((3.141592653589793 * d4) / 32);          // Tube.py:14
             C[12 + tb] = ux;
@@ -664,22 +693,25 @@ __device__ __forceinline__ void reset_envs(const KArgs& a, const LaneId& id, con
         der = env_consts(sc, p.tube_params, n, env, a.use_params != 0, j == 0, gs, LL);
     }
 
-    float q[6];
+    JointLimits lim;
+    if (a.use_params) limits_of_lengths(sc, LL, lim);               // per-env lengths: per-env sampling box and predicates
+    else limits_of_system(sc, lim);
+    float q[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     bool do_fk = valid;
     int tries = 0;
     bool ok = true;
     if (which == 0) {
         if (goal) do_fk = false;                                     // ctr_reach_env.py:102-103
-        else tries = sample_goal(sc, a.key, env_lo, env_hi, episode, 0u, q, ok);   // :100
+        else tries = sample_goal(lim, a.key, env_lo, env_hi, episode, 0u, q, ok);   // :100
     } else {
-        if (a.resample_joints) tries = sample_goal(sc, a.key, env_lo, env_hi, episode, 1u, q, ok);   // :106
+        if (a.resample_joints) tries = sample_goal(lim, a.key, env_lo, env_hi, episode, 1u, q, ok);   // :106
         else {
 #pragma unroll
             for (int i = 0; i < 6; ++i) q[i] = p.joints[(int64_t)i * n + env];                      // :111
         }
     }
-    if (!do_fk) {
-#pragma unroll
+    if (!do_fk || !ok) {       // stuck sampling (the reference raises, obs.py:204-205): a defined, valid state -- all tubes
+#pragma unroll                 // fully extended, alpha = 0 -- and the ST_GOAL_STUCK counter, which ctr_stats turns into rc 3
         for (int i = 0; i < 6; ++i) q[i] = 0.f;
     }
     double beta[3] = {(double)q[0], (double)q[1], (double)q[2]};
@@ -802,7 +834,9 @@ __global__ void k_set_action(const SysConst* __restrict__ sys, int n_systems, fl
         q[k] = joints[(int64_t)k * n + i];
         a[k] = action[(int64_t)k * n + i];
     }
-    set_action(q, a, s_sys[s], n_substeps);
+    JointLimits lim;
+    limits_of_system(s_sys[s], lim);
+    set_action(q, a, lim, n_substeps);
 #pragma unroll
     for (int k = 0; k < 6; ++k) joints[(int64_t)k * n + i] = q[k];
 }
@@ -854,6 +888,7 @@ struct HostGraph {              // one captured ctr_step_host pipeline (keyed by
     const void* key[8];
     int64_t per;
     bool packed;
+    bool uy0;                   // k_step instantiation captured in the kernel nodes (U_y == 0 fast path or generic)
     uint64_t stamp;
     cudaGraph_t graph;
     cudaGraphExec_t exec;
@@ -882,6 +917,8 @@ struct ctr_handle {
     int host_chunks;           // chunks per ctr_step_host call (0: one per 16384 envs, at most 16); $CTR_HOST_CHUNKS
     int host_graphs;           // replay the pipeline as a CUDA graph (default; $CTR_HOST_GRAPH=0 submits call by call)
     cudaEvent_t ev_fork, ev_join[N_COMPUTE_STREAMS + 1], ev_chunk[16];
+    cudaEvent_t ev_user;       // recorded on the caller's stream by every device-pointer call that changes env state
+    int user_pending;          // ... and waited for by the next *_host call, which runs on the handle's private streams
     std::vector<HostGraph> graphs;
     uint64_t graph_clock;
     int use_params;
@@ -921,7 +958,6 @@ void derive_system(const double tube[3][8], int constrain_alpha, SysConst& sc) {
         sc.low[3 + i] = constrain_alpha ? -PI_F : -INFINITY;         // obs.py:64-75
         sc.high[3 + i] = constrain_alpha ? PI_F : INFINITY;
         sc.Lf[i] = (float)t[0];
-        sc.slow[i] = sc.low[i];
         const double k = (sc.EI[i] != 0.0) ? sc.EI[i] / sc.GJ[i] : 0.0;   // model.py:101
         sc.der[DER_EI + i] = sc.EI[i];
         sc.der[DER_EIUX + i] = sc.EI[i] * sc.Ux[i];
@@ -964,6 +1000,11 @@ KArgs make_args(const ctr_handle* h) {
     a.rtol = h->cfg.rtol;
     a.atol = h->cfg.atol;
     a.domain_rand = h->cfg.domain_rand;
+    a.domain_rand_length = h->cfg.domain_rand > 0.0 ? h->cfg.domain_rand_length : 0.0;
+    a.act_lim_ext = (float)h->cfg.extension_action_limit;                          // np.full(3, limit) in a float32 Box
+    a.act_lim_rot = (float)(h->cfg.rotation_action_limit_deg * (M_PI / 180.0));    // np.deg2rad(limit) -> float32
+    a.action_scale = h->cfg.action_scale;
+    a.action_clip = h->cfg.action_clip;
     a.key = make_uint2((unsigned)h->cfg.seed, (unsigned)(h->cfg.seed >> 32));
     a.env_offset = h->cfg.env_offset;
     a.act_stride_field = h->n;
@@ -979,6 +1020,22 @@ KArgs make_args(const ctr_handle* h) {
     a.perm = h->perm;
     a.win_count = h->win_count;
     return a;
+}
+
+// Stream contract (include/ctr_b200.h): device-pointer calls run on the caller's stream, *_host calls on the handle's private
+// streams.  mark_user_work() is called after a device-pointer call that writes env state; order_after_user() makes the private
+// stream wait for it, so that `ctr_reset(stream); ctr_step_host(...)` needs no synchronisation by the caller.
+int mark_user_work(ctr_handle* h, cudaStream_t st) {
+    if (st == h->streams[0]) return 0;
+    CTR_CUDA(cudaEventRecord(h->ev_user, st));
+    h->user_pending = 1;
+    return 0;
+}
+int order_after_user(ctr_handle* h, cudaStream_t priv) {
+    if (!h->user_pending) return 0;
+    CTR_CUDA(cudaStreamWaitEvent(priv, h->ev_user, 0));
+    h->user_pending = 0;
+    return 0;
 }
 
 inline int grid_for(int64_t n_envs) { return (int)((n_envs + ENVS_PER_BLOCK - 1) / ENVS_PER_BLOCK); }
@@ -1050,6 +1107,9 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     if (cfg->precision != CTR_PRECISION_F64 && cfg->precision != CTR_PRECISION_F32) CTR_FAIL("unknown precision");
     if (cfg->integrator == CTR_INTEGRATOR_RK4 && cfg->rk4_steps < 1) CTR_FAIL("rk4_steps must be >= 1");
     if (cfg->n_substeps < 0 || cfg->max_steps_per_episode < 1) CTR_FAIL("bad n_substeps / max_steps_per_episode");
+    if (!(cfg->domain_rand_length >= 0.0 && cfg->domain_rand_length < 0.5)) CTR_FAIL("domain_rand_length must be in [0, 0.5)");
+    if (cfg->domain_rand_length > 0.0 && !(cfg->domain_rand > 0.0))
+        CTR_FAIL("domain_rand_length needs domain_rand > 0 (lengths are drawn with the other tube parameters at reset)");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) CTR_FAIL("no CUDA device available (this library has no CPU fallback)");
@@ -1163,6 +1223,8 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     h->host_flags_late = getenv("CTR_HOST_FLAGS_LATE") ? atoi(getenv("CTR_HOST_FLAGS_LATE")) : 1;
     h->graph_clock = 0;
     CTR_CUDA(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+    CTR_CUDA(cudaEventCreateWithFlags(&h->ev_user, cudaEventDisableTiming));
+    h->user_pending = 0;
     void* f[CTR_F_COUNT] = {h->p.joints, h->p.desired_goal, h->p.desired_joints, h->p.starting_joints,
                             h->p.starting_position, h->p.achieved, h->p.orientation, h->p.t, h->p.system, h->p.episode,
                             h->p.obs, h->p.reward, h->p.done, h->p.success, h->p.error, h->p.terminal_obs,
@@ -1197,6 +1259,7 @@ int ctr_destroy(ctr_handle* h) {
         cudaGraphDestroy(g.graph);
     }
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_user) cudaEventDestroy(h->ev_user);
     const cudaError_t pending = cudaGetLastError();      // never hand a stale error to the next handle's first launch check
     delete h;
     if (pending != cudaSuccess) {
@@ -1256,12 +1319,12 @@ int ctr_set_tube_params(ctr_handle* h, const double* params_dev, void* stream) {
         CTR_CUDA(cudaMemsetAsync(h->p.pf_episode, 0, sizeof(uint32_t) * h->n, (cudaStream_t)stream));
     if (!params_dev) {
         h->use_params = 0;
-        return 0;
+        return mark_user_work(h, (cudaStream_t)stream);
     }
     CTR_CUDA(cudaMemcpyAsync(h->p.tube_params, params_dev, sizeof(double) * 18 * h->n, cudaMemcpyDeviceToDevice,
                              (cudaStream_t)stream));
     h->use_params = 1;
-    return 0;
+    return mark_user_work(h, (cudaStream_t)stream);
 }
 
 int ctr_fk(ctr_handle* h, const double* joints_dev, const int32_t* system_dev, const double* params_dev, int64_t n,
@@ -1344,11 +1407,13 @@ int ctr_reset(ctr_handle* h, const uint8_t* mask_dev, const double* goal_dev, co
         k_mask_to_list<<<(int)((h->n + 255) / 256), 256, 0, st>>>(mask_dev, h->n, h->p.reset_list, h->p.reset_count);
         h->launches += 1;
         CTR_CUDA(cudaGetLastError());
-        return launch_reset(h, h->p.reset_list, h->p.reset_count, h->n, goal_dev, system_dev, st);
+        int rc = launch_reset(h, h->p.reset_list, h->p.reset_count, h->n, goal_dev, system_dev, st);
+        return rc ? rc : mark_user_work(h, st);
     }
     // full reset: every env re-queues itself, so drop what the queue holds (keeps it within capacity)
     if (h->prefetch) CTR_CUDA(cudaMemsetAsync(h->p.rq_ctr + (h->step_index % 3), 0, sizeof(int32_t), st));
-    return launch_reset(h, nullptr, nullptr, h->n, goal_dev, system_dev, st);
+    int rc = launch_reset(h, nullptr, nullptr, h->n, goal_dev, system_dev, st);
+    return rc ? rc : mark_user_work(h, st);
 }
 
 int ctr_step(ctr_handle* h, const float* action_dev, void* stream) {
@@ -1383,7 +1448,7 @@ int ctr_step_strided(ctr_handle* h, const float* action_dev, int64_t stride_fiel
     // leading blocks drain the refill queue of the previous step first (see k_step)
     int rc = launch_step_range(h, a, action_dev, 0, h->n, h->prefetch ? h->sm_count : 0, (cudaStream_t)stream);
     h->step_index += 1;
-    return rc;
+    return rc ? rc : mark_user_work(h, (cudaStream_t)stream);
 }
 
 static int copy_out(ctr_handle* h, cudaStream_t st, double* obs, double* ach, double* des, double* rew, uint8_t* done,
@@ -1493,6 +1558,10 @@ static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_h
     per = ((per + SORT_WINDOW - 1) / SORT_WINDOW) * SORT_WINDOW;      // chunks start on sorting-window boundaries
     const KArgs a = make_args(h);
     cudaStream_t s0 = h->streams[0];
+    {   // env state written by device-pointer calls on the caller's stream (reset, step, tube parameters) comes first
+        int rc = order_after_user(h, s0);
+        if (rc) return rc;
+    }
     if (!h->host_graphs) {
         int rc = enqueue_host_step(h, a, per, action_host, obs_host, achieved_host, desired_host, reward_host, done_host,
                                    success_host, error_host, packed);
@@ -1502,9 +1571,12 @@ static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_h
         return 0;
     }
     const void* key[8] = {action_host, obs_host, achieved_host, desired_host, reward_host, done_host, success_host, error_host};
+    // the captured kernel nodes keep the k_step instantiation chosen at capture time (launch_step_range): a capture made
+    // before ctr_set_tube_params() switched per-env constants on (or off) must not be replayed afterwards
+    const bool uy0 = h->all_uy_zero && !h->use_params;
     HostGraph* g = nullptr;
     for (auto& c : h->graphs)
-        if (c.per == per && c.packed == packed && memcmp(c.key, key, sizeof key) == 0) g = &c;
+        if (c.per == per && c.packed == packed && c.uy0 == uy0 && memcmp(c.key, key, sizeof key) == 0) g = &c;
     if (!g) {
         if (h->graphs.size() >= 8) {                 // evict the least recently used capture
             size_t old = 0;
@@ -1518,6 +1590,7 @@ static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_h
         memcpy(ng.key, key, sizeof key);
         ng.per = per;
         ng.packed = packed;
+        ng.uy0 = uy0;
         ng.stamp = 0;
         cudaGraph_t graph = nullptr;
         const int64_t launches0 = h->launches;
@@ -1590,7 +1663,9 @@ static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_h
 
 int ctr_reset_host(ctr_handle* h, double* obs_host, double* achieved_host, double* desired_host) {
     if (!h) CTR_FAIL("null handle");
-    int rc = ctr_reset(h, nullptr, nullptr, nullptr, h->stream);
+    int rc = order_after_user(h, h->stream);
+    if (rc) return rc;
+    rc = ctr_reset(h, nullptr, nullptr, nullptr, h->stream);
     if (rc) return rc;
     return copy_out(h, h->stream, obs_host, achieved_host, desired_host, nullptr, nullptr, nullptr, nullptr);
 }
@@ -1643,6 +1718,19 @@ int ctr_work_counters(ctr_handle* h, double out4_host[4], void* stream) {
     out4_host[1] = tmp[ST_ATTEMPTS];
     out4_host[2] = tmp[ST_SECTIONS];
     out4_host[3] = tmp[ST_FK_COUNT];
+    return 0;
+}
+
+int ctr_fault_counters(ctr_handle* h, double out4_host[4], void* stream) {
+    if (!h || !out4_host) CTR_FAIL("null argument");
+    CTR_CUDA(cudaSetDevice(h->device));
+    double tmp[N_STATS];
+    CTR_CUDA(cudaMemcpyAsync(tmp, h->p.stats, sizeof(tmp), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    CTR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    out4_host[0] = tmp[ST_FK_FAILED];
+    out4_host[1] = tmp[ST_GOAL_STUCK];
+    out4_host[2] = tmp[ST_INVALID_ACTION];
+    out4_host[3] = 0.0;
     return 0;
 }
 

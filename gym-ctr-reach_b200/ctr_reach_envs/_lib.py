@@ -8,7 +8,7 @@ import numpy as np
 _ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.environ.get('CTR_B200_LIB') or os.path.join(_ROOT, 'libctr_b200.so')   # override: kernel-variant experiments
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 MAX_SYSTEMS = 8
 
 REP = {'egocentric': 0, 'proprioceptive': 1}
@@ -25,7 +25,7 @@ EXPORTS = ['ctr_last_error', 'ctr_abi_version', 'ctr_create', 'ctr_destroy', 'ct
            'ctr_system_constants', 'ctr_set_tolerance', 'ctr_get_tolerance', 'ctr_seed', 'ctr_set_tube_params', 'ctr_fk',
            'ctr_fk_host', 'ctr_set_action', 'ctr_set_state_host', 'ctr_reset', 'ctr_step', 'ctr_step_strided',
            'ctr_step_host', 'ctr_step_host_packed', 'ctr_reset_host', 'ctr_compute_reward', 'ctr_relabel', 'ctr_stats', 'ctr_stats_reset',
-           'ctr_launch_count', 'ctr_work_counters', 'ctr_measure_fma_peak', 'ctr_her_begin', 'ctr_her_store',
+           'ctr_launch_count', 'ctr_work_counters', 'ctr_fault_counters', 'ctr_measure_fma_peak', 'ctr_her_begin', 'ctr_her_store',
            'ctr_her_sample', 'ctr_fk_shape', 'ctr_jacobian', 'ctr_ik_dls']
 
 
@@ -52,6 +52,9 @@ class CtrConfig(ctypes.Structure):
         ('domain_rand', ctypes.c_double),
         ('seed', ctypes.c_uint64),
         ('env_offset', ctypes.c_int64),
+        ('domain_rand_length', ctypes.c_double),
+        ('action_scale', ctypes.c_int32),
+        ('action_clip', ctypes.c_int32),
     ]
 
 
@@ -115,6 +118,7 @@ def load():
     lib.ctr_stats.argtypes = [vp, vp, vp]
     lib.ctr_stats_reset.argtypes = [vp, vp]
     lib.ctr_work_counters.argtypes = [vp, vp, vp]
+    lib.ctr_fault_counters.argtypes = [vp, vp, vp]
     lib.ctr_measure_fma_peak.argtypes = [i32, i32, ctypes.POINTER(f64)]
     lib.ctr_launch_count.restype = i64
     lib.ctr_launch_count.argtypes = [vp]
@@ -146,7 +150,8 @@ def check(rc):
 def make_config(systems, n_substeps=10, max_steps_per_episode=150, joint_representation='egocentric',
                 constrain_alpha=False, extension_action_limit=0.001, rotation_action_limit=5, resample_joints=True,
                 auto_reset=True, integrator='dp45', precision='f64', rk4_steps=8, reward_mode='sparse', rtol=1e-3,
-                atol=1e-6, initial_tol=0.02, domain_rand=0.0, seed=0, env_offset=0):
+                atol=1e-6, initial_tol=0.02, domain_rand=0.0, seed=0, env_offset=0, domain_rand_length=0.0, action_scale=False,
+                action_clip=False):
     """systems: float64 [n_systems][3][8] in Tube argument order (Tube.py:7-8)."""
     systems = np.ascontiguousarray(systems, dtype=np.float64).reshape(-1, 3, 8)
     if not 1 <= systems.shape[0] <= MAX_SYSTEMS:
@@ -175,6 +180,9 @@ def make_config(systems, n_substeps=10, max_steps_per_episode=150, joint_represe
     cfg.domain_rand = float(domain_rand)
     cfg.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
     cfg.env_offset = int(env_offset)
+    cfg.domain_rand_length = float(domain_rand_length)
+    cfg.action_scale = int(bool(action_scale))
+    cfg.action_clip = int(bool(action_clip))
     return cfg
 
 

@@ -66,7 +66,11 @@ class CtrReachVecEnv(object):
 
     num_envs, device, integrator ('dp45' = scipy-RK45 parity mode | 'rk4'), precision ('f64' | 'f32'), rk4_steps,
     reward_mode ('sparse' = reference | 'dense' = -distance), auto_reset, seed, env_offset (global index of env 0,
-    for multi-GPU shards: results do not depend on how the env range is partitioned).
+    for multi-GPU shards: results do not depend on how the env range is partitioned), and three extensions that default to
+    the reference's behaviour: domain_rand_length (+-fraction on the tube lengths at every reset, with per-env joint limits;
+    needs domain_rand > 0), action_scale (actions in [-1, 1] x the action limits), action_clip (clip / zero invalid action
+    components instead of passing them through).  Where the reference asserts on an action (ctr_reach_env.py:131-132) the
+    batch counts: fault_counters()['invalid_actions'].
 
     Tensors returned by reset()/step() are views of device buffers that the next step()/reset() overwrites; layouts are
     (N, D) views of SoA [D][N] storage.
@@ -76,7 +80,8 @@ class CtrReachVecEnv(object):
                  joint_representation, initial_joints, constrain_alpha, extension_action_limit, rotation_action_limit,
                  max_steps_per_episode, n_substeps, evaluation, select_systems, resample_joints=True,
                  length_based_sample=False, domain_rand=0.0, device=0, integrator='dp45', precision='f64', rk4_steps=8,
-                 reward_mode='sparse', auto_reset=True, seed=0, env_offset=0, rtol=1e-3, atol=1e-6):
+                 reward_mode='sparse', auto_reset=True, seed=0, env_offset=0, rtol=1e-3, atol=1e-6, domain_rand_length=0.0,
+                 action_scale=False, action_clip=False):
         assert joint_representation in ['egocentric', 'proprioceptive']
         if length_based_sample:
             # the reference branch reads a non-existent attribute and raises (ctr_reach_env.py:84-92)
@@ -99,6 +104,8 @@ class CtrReachVecEnv(object):
         self.resample_joints = resample_joints
         self.length_based_sample = length_based_sample
         self.domain_rand = domain_rand
+        self.domain_rand_length = domain_rand_length
+        self.action_scale, self.action_clip = bool(action_scale), bool(action_clip)
         self.initial_joints = np.asarray(initial_joints)
         self.extension_action_limit = extension_action_limit
         self.rotation_action_limit = rotation_action_limit
@@ -107,6 +114,9 @@ class CtrReachVecEnv(object):
         self.goal_tolerance = GoalTolerance(goal_tolerance_parameters)
         self.observation_space, self.action_space = build_spaces(
             self.tube_lengths, self.goal_tolerance, self.num_systems, extension_action_limit, rotation_action_limit)
+        self.action_limits = self.action_space.high.copy()      # joint deltas per step (float32), whatever the action convention
+        if self.action_scale:                                   # a policy's normalised output
+            self.action_space = Box(low=-np.ones(6), high=np.ones(6), dtype="float32")
 
         cfg = _lib.make_config(self.systems, n_substeps=n_substeps, max_steps_per_episode=max_steps_per_episode,
                                joint_representation=joint_representation, constrain_alpha=constrain_alpha,
@@ -114,7 +124,8 @@ class CtrReachVecEnv(object):
                                resample_joints=resample_joints, auto_reset=auto_reset, integrator=integrator,
                                precision=precision, rk4_steps=rk4_steps, reward_mode=reward_mode, rtol=rtol, atol=atol,
                                initial_tol=self.goal_tolerance.get_tol(), domain_rand=domain_rand, seed=seed,
-                               env_offset=env_offset)
+                               env_offset=env_offset, domain_rand_length=domain_rand_length, action_scale=action_scale,
+                               action_clip=action_clip)
         h = ctypes.c_void_p()
         _lib.check(self.lib.ctr_create(ctypes.byref(cfg), self.num_envs, self.device.index, ctypes.byref(h)))
         self.handle = h
@@ -335,6 +346,12 @@ class CtrReachVecEnv(object):
         out = (ctypes.c_double * 4)()
         _lib.check(self.lib.ctr_work_counters(self.handle, out, self._stream()))
         return dict(zip(('nfev', 'attempts', 'sections', 'fk_solves'), list(out)))
+
+    def fault_counters(self):
+        """What the reference raises on, counted since the last stats_reset(): dict(fk_failed, goal_stuck, invalid_actions)."""
+        out = (ctypes.c_double * 4)()
+        _lib.check(self.lib.ctr_fault_counters(self.handle, out, self._stream()))
+        return dict(zip(('fk_failed', 'goal_stuck', 'invalid_actions'), list(out)[:3]))
 
     def alloc_host_outputs(self):
         """Pinned host arrays for step_host(), laid out like the device's result block (observation | achieved_goal |

@@ -12,7 +12,11 @@
  *  - "dev" pointers are device pointers on the handle's device, "host" pointers are host memory
  *    (pinned or pageable).  Batched arrays are SoA: [field][n] (field-major, n contiguous).
  *  - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Device-pointer
- *    calls are asynchronous on that stream; *_host calls synchronise before returning.
+ *    calls are asynchronous on that stream.  *_host calls run on the handle's own non-blocking
+ *    streams and synchronise before returning; they are ordered AFTER every earlier device-pointer
+ *    call that writes env state (ctr_reset, ctr_step*, ctr_set_tube_params), whatever stream that
+ *    call was given, so `ctr_reset(h, .., stream); ctr_step_host(h, ..)` needs no synchronisation
+ *    by the caller.  Mixing streams between two device-pointer calls is the caller's to order.
  *  - there is NO CPU fallback: without a CUDA device ctr_create fails.
  */
 #ifndef CTR_B200_H
@@ -24,7 +28,7 @@
 extern "C" {
 #endif
 
-#define CTR_ABI_VERSION 1
+#define CTR_ABI_VERSION 2
 #define CTR_MAX_SYSTEMS 8
 #define CTR_NUM_TUBES 3
 #define CTR_TUBE_FIELDS 8   /* length, length_curved, diameter_inner, diameter_outer, stiffness,
@@ -61,6 +65,15 @@ typedef struct ctr_config {
     double domain_rand;                  /* +-fraction on d_i, d_o, E, G, Ux at every reset (model_utils.py:15-19) */
     uint64_t seed;                       /* Philox key */
     int64_t env_offset;                  /* global index of this handle's env 0 (multi-GPU shards) */
+    /* --- extensions beyond the reference (all 0 = reference behaviour) --- */
+    double domain_rand_length;           /* +-fraction on L and L_c at every reset, needs domain_rand > 0; the joint limits,
+                                            ordering constants and goal-sampling box then follow each env's own lengths
+                                            (the reference forbids length randomisation, model_utils.py:12-14) */
+    int32_t action_scale;                /* 1: actions arrive in [-1, 1] (a policy's output) and are multiplied by
+                                            extension_action_limit / rotation_action_limit (ctr_reach_env.py:55-62) */
+    int32_t action_clip;                 /* 1: out-of-Box action components are clipped and NaN components zeroed;
+                                            0: passed through as given.  Either way every env whose action fails the
+                                            reference's asserts (ctr_reach_env.py:131-132) is counted, ctr_fault_counters */
 } ctr_config;
 
 typedef struct ctr_handle ctr_handle;
@@ -173,6 +186,10 @@ int ctr_stats_reset(ctr_handle *h, void *stream);
 /* FK work since the last ctr_stats_reset: [RHS evaluations, RK step attempts, sections, FK solves] (roofline
  * accounting: algorithmic flops = nfev*120 + attempts*1290 + sections*200). */
 int ctr_work_counters(ctr_handle *h, double out4_host[4], void *stream);
+/* Where the reference raises per env, a batch counts (since the last ctr_stats_reset): out4 = FK solves that failed
+ * (model.py:69 / :152-153), goal samplings stuck after 1001 draws (obs.py:204-205), env-steps whose action was NaN or
+ * outside the action Box (ctr_reach_env.py:131-132), 0. */
+int ctr_fault_counters(ctr_handle *h, double out4_host[4], void *stream);
 
 /* Measured FMA-pipe peak of `device` in TFLOP/s (register-resident FMA chains; precision = CTR_PRECISION_*):
  * the roofline denominator of the FK kernels. */

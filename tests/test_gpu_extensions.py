@@ -1,0 +1,147 @@
+"""GPU tests of the extensions `north_star` names beyond the reference: per-env tube LENGTHS with per-env joint limits
+(BASELINE.json config 5), normalised actions, and the batch form of the reference's action asserts
+(ctr_reach_env.py:131-132).  All through the C-ABI; the checker is the C / numpy oracle."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _per_env_systems(oracle_py, rng, n, r_len):
+    """n copies of system 0 whose tube lengths / curved lengths are drawn +-r_len around nominal."""
+    systems = np.repeat(oracle_py.DEFAULT_SYSTEMS[:1], n, axis=0).copy()
+    systems[:, :, 0] *= rng.uniform(1 - r_len, 1 + r_len, size=(n, 3))
+    systems[:, :, 1] *= rng.uniform(1 - r_len, 1 + r_len, size=(n, 3))
+    return systems
+
+
+def test_per_env_lengths_give_per_env_joint_limits(oracle_c, oracle_py, vec_factory):
+    """ctr_set_tube_params with per-env L: Obs.set_action's clip box and ordering constants follow each env's own lengths
+    (obs.py:59-75,181 evaluated per env), bit-exact against the oracle run with one 'system' per env."""
+    n = 6000
+    rng = np.random.RandomState(21)
+    systems = _per_env_systems(oracle_py, rng, n, 0.08)
+    tcs = oracle_c.derive(systems)
+    env = vec_factory(n, auto_reset=False, seed=5)
+    env.reset()
+    env.set_tube_params(tcs)
+    # start from joints at / beyond the per-env limits so that every constraint is active somewhere
+    L = tcs[:, :3]
+    q0 = env.buffer('joints').t().cpu().numpy().copy()
+    q0[: n // 2, :3] = (-L[: n // 2] + 1e-3 + rng.uniform(-2e-3, 2e-3, size=(n // 2, 3))).astype(np.float32)
+    env.set_state(joints=q0)
+    lim = env.action_space.high
+    q = q0.copy()
+    for _ in range(4):
+        act = rng.uniform(-lim, lim, size=(n, 6)).astype(np.float32)
+        act[:, :3] = -np.abs(act[:, :3]) if _ % 2 == 0 else act[:, :3]            # push towards the lower limits
+        obs, *_rest = env.step(torch.tensor(act, device='cuda'))
+        torch.cuda.synchronize()
+        q = oracle_c.set_action_batch(q, act, np.arange(n, dtype=np.int32), L, False, 10)
+        got = env.buffer('joints').t().cpu().numpy()
+        assert np.array_equal(got, q)
+        ref = oracle_c.fk_batch(tcs, q, np.arange(n, dtype=np.int32))
+        assert np.abs(obs['achieved_goal'].cpu().numpy() - ref['tip']).max() < 1e-10
+    low = (-L + 1e-3).astype(np.float32)
+    assert (q[:, :3] >= low).all() and (q[:, :3] <= 0).all()
+    assert (q[:, :3] == low).any(), "no env reached its own lower limit: the test would not see a wrong box"
+    # the nominal box would have been wrong for a good part of the envs
+    nominal_low = (-oracle_c.derive(oracle_py.DEFAULT_SYSTEMS[:1])[0][:3] + 1e-3).astype(np.float32)
+    assert (q[:, :3] < nominal_low).any()
+
+
+def test_domain_rand_length_resets_sample_inside_per_env_limits(oracle_c, oracle_py, vec_factory):
+    """domain_rand_length: L and L_c drawn at every reset; the goal / start sampling box and the nesting predicates
+    (obs.py:59-63,198-200) use the env's own lengths; tips follow the env's own constants."""
+    n = 8000
+    r = 0.06
+    env = vec_factory(n, domain_rand=0.05, domain_rand_length=r, seed=9)
+    env.reset()
+    torch.cuda.synchronize()
+    P = env.buffer('tube_params').t().cpu().numpy()
+    nom = oracle_c.derive(oracle_py.DEFAULT_SYSTEMS[:1])[0]
+    for k in range(6):                                                   # L[3], Lc[3] inside the +-r box, actually spread
+        ratio = P[:, k] / nom[k]
+        assert ratio.min() >= 1 - r - 1e-12 and ratio.max() <= 1 + r + 1e-12 and ratio.std() > 0.4 * r
+    L = P[:, :3]
+    Lf = L.astype(np.float32)
+    low = (-L + 1e-3).astype(np.float32)
+    for name in ('joints', 'desired_joints'):
+        q = env.buffer(name).t().cpu().numpy()
+        b = q[:, :3]
+        assert (b >= low).all() and (b <= 0).all(), name
+        assert (b[:, 0] <= b[:, 1]).all() and (b[:, 1] <= b[:, 2]).all(), name
+        assert ((b[:, 0] + Lf[:, 0]) >= (Lf[:, 1] + b[:, 1])).all() and ((b[:, 1] + Lf[:, 1]) >= (Lf[:, 2] + b[:, 2])).all(), name
+        assert np.abs(q[:, 3:]).max() <= np.float32(np.pi)
+    idx = np.arange(n, dtype=np.int32)
+    ref = oracle_c.fk_batch(P, env.buffer('joints').t().cpu().numpy(), idx)
+    assert np.abs(env.buffer('achieved_goal').t().cpu().numpy() - ref['tip']).max() < 1e-10
+    refg = oracle_c.fk_batch(P, env.buffer('desired_joints').t().cpu().numpy(), idx)
+    assert np.abs(env.buffer('desired_goal').t().cpu().numpy() - refg['tip']).max() < 1e-10
+    # a step keeps using the env's own box (auto-reset envs excluded: they carry the next episode's draw)
+    lim = env.action_space.high
+    act = np.tile(np.array([-1e-3, -1e-3, -1e-3, 0, 0, 0], dtype=np.float32), (n, 1))
+    q0 = env.buffer('joints').t().cpu().numpy().copy()
+    _, _, done, _ = env.step(torch.tensor(act, device='cuda'))
+    torch.cuda.synchronize()
+    keep = ~done.bool().cpu().numpy()
+    q1 = oracle_c.set_action_batch(q0, act, idx, L, False, 10)
+    assert keep.sum() > n // 2 and np.array_equal(env.buffer('joints').t().cpu().numpy()[keep], q1[keep])
+    # config check: lengths need domain_rand
+    with pytest.raises(Exception):
+        vec_factory(16, domain_rand=0.0, domain_rand_length=0.05)
+
+
+def test_action_scale_equals_scaled_raw_actions(vec_factory):
+    n = 4096
+    a, b = vec_factory(n, seed=3, action_scale=True), vec_factory(n, seed=3)
+    assert np.array_equal(a.action_space.high, np.ones(6, dtype=np.float32))
+    assert np.array_equal(a.action_limits, b.action_space.high)
+    for e in (a, b):
+        e.reset()
+    rng = np.random.RandomState(4)
+    lim = b.action_space.high
+    for _ in range(5):
+        u = rng.uniform(-1, 1, size=(n, 6)).astype(np.float32)
+        raw = (u * lim).astype(np.float32)                               # float32 product, as the kernel forms it
+        oa, ra, da, _ia = a.step(torch.tensor(u, device='cuda'))
+        ob, rb, db, _ib = b.step(torch.tensor(raw, device='cuda'))
+        torch.cuda.synchronize()
+        assert torch.equal(a.buffer('joints'), b.buffer('joints'))
+        assert torch.equal(oa['observation'], ob['observation']) and torch.equal(ra, rb) and torch.equal(da, db)
+    assert a.fault_counters()['invalid_actions'] == 0 and b.fault_counters()['invalid_actions'] == 0
+
+
+def test_invalid_actions_are_counted_and_optionally_clipped(vec_factory):
+    """ctr_reach_env.py:131-132 asserts `not all NaN` and `action_space.contains(action)`; the batch counts such env-steps
+    (any NaN or out-of-Box component) and, with action_clip, replaces them by the clipped / zeroed action."""
+    n = 2000
+    rng = np.random.RandomState(8)
+    env, clip, ref = vec_factory(n, seed=2, auto_reset=False), vec_factory(n, seed=2, auto_reset=False, action_clip=True), \
+        vec_factory(n, seed=2, auto_reset=False)
+    for e in (env, clip, ref):
+        e.reset()
+        e.stats_reset()
+    lim = env.action_space.high
+    act = rng.uniform(-lim, lim, size=(n, 6)).astype(np.float32)
+    bad_nan = rng.choice(n, 37, replace=False)
+    bad_big = np.setdiff1d(rng.choice(n, 80, replace=False), bad_nan)
+    act[bad_nan, rng.randint(0, 6, size=bad_nan.size)] = np.nan
+    act[bad_big, 0] = 3 * lim[0]
+    act[bad_big, 4] = -2 * lim[4]
+    fixed = np.clip(np.nan_to_num(act, nan=0.0), -lim, lim)
+    env.step(torch.tensor(act, device='cuda'))
+    clip.step(torch.tensor(act, device='cuda'))
+    ref.step(torch.tensor(fixed, device='cuda'))
+    torch.cuda.synchronize()
+    want = float(bad_nan.size + bad_big.size)
+    assert env.fault_counters()['invalid_actions'] == want and clip.fault_counters()['invalid_actions'] == want
+    assert ref.fault_counters()['invalid_actions'] == 0
+    assert torch.equal(clip.buffer('joints'), ref.buffer('joints'))
+    assert torch.equal(clip.buffer('achieved_goal'), ref.buffer('achieved_goal'))
+    good = np.ones(n, dtype=bool)
+    good[bad_nan] = good[bad_big] = False
+    assert torch.equal(env.buffer('joints')[:, good], ref.buffer('joints')[:, good])     # valid actions are untouched
+    env.stats_reset()
+    assert env.fault_counters()['invalid_actions'] == 0

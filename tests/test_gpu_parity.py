@@ -39,7 +39,7 @@ ALL4 = dict(select_systems=[0, 1, 2, 3])
 def test_library_loaded_is_in_tree():
     from ctr_reach_envs import _lib
     lib = _lib.load()
-    assert lib.ctr_abi_version() == 1
+    assert lib.ctr_abi_version() == 2
     assert _lib.LIB_PATH.endswith('gym-ctr-reach_b200/libctr_b200.so')
 
 
@@ -614,6 +614,58 @@ def test_host_step_entry_point_matches_device_path(vec_factory, monkeypatch):
             assert torch.equal(envs[0].buffer(k), envs[1].buffer(k)), k
 
 
+def test_host_step_is_ordered_after_device_calls_on_the_callers_stream(vec_factory):
+    """ctr_step_host runs on the handle's private streams; reset / step / set_tube_params run on the caller's
+    stream.  `reset(); step_host()` with NO synchronisation in between must see the reset (the library orders them)."""
+    n = 40000
+    a, b = vec_factory(n, seed=11), vec_factory(n, seed=11)
+    rng = np.random.RandomState(5)
+    lim = a.action_space.high
+    out = b.alloc_host_outputs()
+    for rep in range(3):
+        act = rng.uniform(-lim, lim, size=(n, 6)).astype(np.float32)
+        act_dev = torch.tensor(act, device='cuda')
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):                 # a busy non-default stream: the reset is still queued when step_host starts
+            b.reset()
+            b.step(act_dev)
+            b.step_host(np.ascontiguousarray(act.T), out)          # no synchronize between the three calls
+        a.reset()
+        a.step(act_dev)
+        obs, reward, done, info = a.step(act_dev)
+        torch.cuda.synchronize()
+        assert np.array_equal(out['observation'].T, obs['observation'].cpu().numpy())
+        assert np.array_equal(out['reward'], reward.cpu().numpy())
+        assert torch.equal(a.buffer('joints'), b.buffer('joints')) and torch.equal(a.buffer('episode'), b.buffer('episode'))
+
+
+def test_host_step_graph_follows_tube_param_switch(oracle_c, oracle_py, vec_factory):
+    """the cached CUDA graph of ctr_step_host keeps the k_step instantiation of capture time; per-env constants
+    with U_y != 0 switched on afterwards must not be replayed through the U_y == 0 kernel."""
+    n = 1280
+    rng = np.random.RandomState(6)
+    systems = np.stack([oracle_py.randomize_system(rng, oracle_py.DEFAULT_SYSTEMS[0], 0.05) for _ in range(n)])
+    systems[:, :, 7] = rng.uniform(1.0, 8.0, size=(n, 3))           # y_curvature != 0: only the generic kernel is right
+    tcs = oracle_c.derive(systems)
+    a, b = vec_factory(n, seed=12, auto_reset=False), vec_factory(n, seed=12, auto_reset=False)
+    for e in (a, b):
+        e.reset()
+    lim = a.action_space.high
+    out = b.alloc_host_outputs()
+    for phase, params in enumerate((None, tcs, None)):
+        for e in (a, b):
+            e.set_tube_params(params)
+        for _ in range(2):
+            act = rng.uniform(-lim, lim, size=(n, 6)).astype(np.float32)
+            obs, *_ = a.step(torch.tensor(act, device='cuda'))
+            torch.cuda.synchronize()
+            b.step_host(np.ascontiguousarray(act.T), out)            # same host pointers every time: same graph key otherwise
+            assert np.array_equal(out['achieved_goal'].T, obs['achieved_goal'].cpu().numpy()), phase
+        if params is not None:
+            ref = oracle_c.fk_batch(tcs, a.buffer('joints').t().cpu().numpy(), np.arange(n, dtype=np.int32))
+            assert np.abs(out['achieved_goal'].T - ref['tip']).max() < 1e-10
+
+
 def test_backbone_shape_vs_reference_and_oracle(golden, oracle_c, tube_constants, vec_factory):
     """ctr_fk_shape against the reference's Model.r / tip_pos fixture: same number of samples, identical
     split indices, positions within 1e-10 m (bar 1e-5 m); the last sample is the tip ctr_fk returns; r1/r2/r3 slice alike."""
@@ -788,7 +840,7 @@ def test_error_paths(vec_factory):
     cfg.abi_version = 99
     assert lib.ctr_create(ctypes.byref(cfg), 4, 0, ctypes.byref(h)) != 0
     assert b'abi_version' in lib.ctr_last_error()
-    cfg.abi_version = 1
+    cfg.abi_version = 2
     assert lib.ctr_create(ctypes.byref(cfg), 0, 0, ctypes.byref(h)) != 0
     assert lib.ctr_create(ctypes.byref(cfg), 4, 999, ctypes.byref(h)) != 0
     env = vec_factory(16)

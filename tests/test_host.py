@@ -34,7 +34,7 @@ def test_library_exports_every_header_symbol(lib):
     for n in names:
         assert hasattr(so, n), n
     assert sorted(lib.EXPORTS) == names            # the python binding covers the whole header
-    assert lib.load().ctr_abi_version() == 1
+    assert lib.load().ctr_abi_version() == lib.ABI_VERSION == 2
 
 
 def test_config_struct_layout_matches_header(lib, tmp_path):
