@@ -1721,6 +1721,23 @@ int ctr_work_counters(ctr_handle* h, double out4_host[4], void* stream) {
     return 0;
 }
 
+int ctr_debug_buffer(ctr_handle* h, int32_t which, void** dev_ptr, int64_t* count) {
+    if (!h || !dev_ptr || !count) CTR_FAIL("null argument");
+    *dev_ptr = nullptr;
+    *count = 0;
+    switch (which) {
+        case CTR_DBG_PERM: *dev_ptr = h->perm; *count = h->perm ? h->n : 0; break;
+        case CTR_DBG_WINDOW_COUNTERS: *dev_ptr = h->win_count; *count = h->win_count ? (h->n + SORT_WINDOW - 1) / SORT_WINDOW : 0; break;
+        case CTR_DBG_QUEUE_COUNTERS: *dev_ptr = h->prefetch ? h->p.rq_ctr : nullptr; *count = h->prefetch ? 6 : 0; break;
+        case CTR_DBG_QUEUE_0: case CTR_DBG_QUEUE_1: case CTR_DBG_QUEUE_2:
+            *dev_ptr = h->prefetch ? h->p.rq_list[which - CTR_DBG_QUEUE_0] : nullptr; *count = h->prefetch ? h->rq_cap : 0; break;
+        case CTR_DBG_SLOT_TAGS: *dev_ptr = h->prefetch ? h->p.pf_episode : nullptr; *count = h->prefetch ? h->n : 0; break;
+        case CTR_DBG_STEP_INDEX: *dev_ptr = nullptr; *count = h->step_index; break;
+        default: CTR_FAIL("unknown debug buffer");
+    }
+    return 0;
+}
+
 int ctr_fault_counters(ctr_handle* h, double out4_host[4], void* stream) {
     if (!h || !out4_host) CTR_FAIL("null argument");
     CTR_CUDA(cudaSetDevice(h->device));

@@ -25,7 +25,7 @@ EXPORTS = ['ctr_last_error', 'ctr_abi_version', 'ctr_create', 'ctr_destroy', 'ct
            'ctr_system_constants', 'ctr_set_tolerance', 'ctr_get_tolerance', 'ctr_seed', 'ctr_set_tube_params', 'ctr_fk',
            'ctr_fk_host', 'ctr_set_action', 'ctr_set_state_host', 'ctr_reset', 'ctr_step', 'ctr_step_strided',
            'ctr_step_host', 'ctr_step_host_packed', 'ctr_reset_host', 'ctr_compute_reward', 'ctr_relabel', 'ctr_stats', 'ctr_stats_reset',
-           'ctr_launch_count', 'ctr_work_counters', 'ctr_fault_counters', 'ctr_measure_fma_peak', 'ctr_her_begin', 'ctr_her_store',
+           'ctr_launch_count', 'ctr_work_counters', 'ctr_fault_counters', 'ctr_debug_buffer', 'ctr_measure_fma_peak', 'ctr_her_begin', 'ctr_her_store',
            'ctr_her_sample', 'ctr_fk_shape', 'ctr_jacobian', 'ctr_ik_dls']
 
 
@@ -119,6 +119,7 @@ def load():
     lib.ctr_stats_reset.argtypes = [vp, vp]
     lib.ctr_work_counters.argtypes = [vp, vp, vp]
     lib.ctr_fault_counters.argtypes = [vp, vp, vp]
+    lib.ctr_debug_buffer.argtypes = [vp, i32, ctypes.POINTER(vp), ctypes.POINTER(i64)]
     lib.ctr_measure_fma_peak.argtypes = [i32, i32, ctypes.POINTER(f64)]
     lib.ctr_launch_count.restype = i64
     lib.ctr_launch_count.argtypes = [vp]

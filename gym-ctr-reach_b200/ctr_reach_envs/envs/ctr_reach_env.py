@@ -25,14 +25,39 @@ class _TrigObjView(object):
 
 
 class _ModelView(object):
-    """Stands in for `env.model`: forward_kinematics(joint, system) -> tip xyz (model.py:30-70)."""
+    """Stands in for `env.model`: forward_kinematics(joint, system) -> tip xyz (model.py:30-70), and the backbone of the LAST
+    solve as the reference keeps it for its renderer and analysis scripts -- `r` (30 samples per section) and its per-tube
+    slices `r1`, `r2`, `r3` (model.py:66-68, read at ctr_reach_env.py:178-182 and src/utils.py:52-54).  The samples come from
+    ctr_fk_shape (the integrator's dense output) and are computed on first access after a solve, not on every step."""
 
     def __init__(self, env):
         self._env = env
+        self._last = None          # (joints float64[6], system) of the last forward-kinematics solve
+        self._shape = None
+
+    def _note(self, joint, system):
+        self._last = (np.asarray(joint, dtype=np.float64).reshape(6).copy(), int(system))
+        self._shape = None
 
     def forward_kinematics(self, joint, system=0, **kwargs):
+        self._note(joint, system)
         return self._env._vec.forward_kinematics(np.asarray(joint, dtype=np.float64).reshape(1, 6),
                                                  system=[int(system)])[0].cpu().numpy()
+
+    def _backbone(self):
+        if self._last is None:
+            raise AttributeError("'Model' object has no attribute 'r' (no forward_kinematics call yet)")
+        if self._shape is None:
+            q, system = self._last
+            r, npts, tip_idx, _ = self._env._vec.backbone_shape(q.reshape(1, 6), system=[system])
+            r, n, idx = r[0].cpu().numpy(), int(npts[0]), tip_idx[0].cpu().numpy()
+            self._shape = (r[:n].copy(),) + tuple(a.copy() for a in self._env._vec.split_backbone(r, n, idx))
+        return self._shape
+
+    r = property(lambda self: self._backbone()[0])
+    r1 = property(lambda self: self._backbone()[1])
+    r2 = property(lambda self: self._backbone()[2])
+    r3 = property(lambda self: self._backbone()[3])
 
 
 class CtrReachEnv(object):
@@ -105,6 +130,7 @@ class CtrReachEnv(object):
             self.desired_joints = b['desired_joints'][:, 0].copy()
         self.starting_joints = b['starting_joints'][:, 0].copy()
         self.starting_position = b['starting_position'][:, 0].copy()
+        self.model._note(self.trig_obj.joints, self.system)      # ctr_reach_env.py:108: the last solve is the start state
         return self._obs()
 
     def seed(self, seed=None):
@@ -118,6 +144,7 @@ class CtrReachEnv(object):
         a = np.asarray(action, dtype=np.float32).reshape(1, 6)
         self._vec.step(a)
         self.t += 1
+        self.model._note(self.trig_obj.joints, self.system)      # ctr_reach_env.py:137
         b = self._pull(('reward', 'done', 'is_success', 'error'))
         obs = self._obs()
         reward = np.float64(b['reward'][0])
@@ -140,7 +167,13 @@ class CtrReachEnv(object):
         return r if r.ndim else np.float64(r)
 
     def render(self, mode='empty', **kwargs):
-        return None   # the matplotlib live plot (ctr_3d_graph.py) is out of scope
+        """ctr_reach_env.py:172-182.  The reference's 'live' mode hands (t, achieved, desired, r1, r2, r3) to a matplotlib figure
+        (ctr_3d_graph.py; no graphics stack on this box): here the same six values are returned as a dict, headless."""
+        if mode == 'live':
+            obs = self.trig_obj.obs if self.trig_obj.obs is not None else self._obs()
+            return {'t': self.t, 'achieved_goal': obs['achieved_goal'], 'desired_goal': obs['desired_goal'],
+                    'r1': self.model.r1, 'r2': self.model.r2, 'r3': self.model.r3}
+        return None
 
     def close(self):
         self._vec.close()

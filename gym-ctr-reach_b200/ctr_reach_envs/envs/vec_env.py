@@ -353,6 +353,19 @@ class CtrReachVecEnv(object):
         _lib.check(self.lib.ctr_fault_counters(self.handle, out, self._stream()))
         return dict(zip(('fk_failed', 'goal_stuck', 'invalid_actions'), list(out)[:3]))
 
+    def debug_buffer(self, which):
+        """Copy of one of the step path's internal scheduling buffers (ctr_debug_buffer; invariant tests): 0 perm, 1 window
+        counters, 2 queue counters, 3-5 refill queues, 6 slot tags (uint32 as int64), 7 -> the step index (int)."""
+        p, n = ctypes.c_void_p(), ctypes.c_int64()
+        _lib.check(self.lib.ctr_debug_buffer(self.handle, int(which), ctypes.byref(p), ctypes.byref(n)))
+        if which == 7:
+            return int(n.value)
+        if not p.value:
+            return None
+        torch.cuda.synchronize(self.device)
+        t = torch.as_tensor(_DeviceBuffer(p.value, (n.value,), '<i4'), device=self.device).clone()
+        return (t.to(torch.int64) & 0xFFFFFFFF) if which == 6 else t
+
     def alloc_host_outputs(self):
         """Pinned host arrays for step_host(), laid out like the device's result block (observation | achieved_goal |
         desired_goal | reward | error as float64 rows, done | is_success as uint8 rows) so that ctr_step_host moves
@@ -386,12 +399,36 @@ class CtrReachVecEnv(object):
     def launch_count(self):
         return int(self.lib.ctr_launch_count(self.handle))
 
-    # SB-style conveniences
-    def get_attr(self, name, indices=None):
-        return [getattr(self, name)] * self.num_envs
+    # SB-style conveniences (stable_baselines VecEnv.get_attr / env_method / set_attr: one value per selected env)
+    _PER_ENV = {'t': 't', 'system': 'system', 'desired_goal': 'desired_goal', 'desired_joints': 'desired_joints',
+                'starting_joints': 'starting_joints', 'starting_position': 'starting_position', 'joints': 'joints',
+                'achieved_goal': 'achieved_goal'}
 
-    def env_method(self, name, *args, **kwargs):
-        return [getattr(self, name)(*args, **kwargs)] * self.num_envs
+    def _indices(self, indices):
+        if indices is None:
+            return list(range(self.num_envs))
+        if isinstance(indices, (int, np.integer)):
+            return [int(indices)]
+        return [int(i) for i in indices]
+
+    def get_attr(self, name, indices=None):
+        """Per-env values for the attributes the reference keeps per env (t, system, desired_goal, desired_joints,
+        starting_joints, starting_position; also joints, achieved_goal), read from the device; shared attributes
+        (action_space, goal_tolerance, ...) are repeated."""
+        idx = self._indices(indices)
+        if name in self._PER_ENV:
+            buf = self.buffer(self._PER_ENV[name])
+            sel = torch.as_tensor(idx, device=self.device, dtype=torch.long)
+            vals = (buf[:, sel].t() if buf.dim() == 2 else buf[sel]).cpu().numpy()
+            return [v.copy() if isinstance(v, np.ndarray) else v.item() for v in vals]
+        return [getattr(self, name) for _ in idx]
+
+    def env_method(self, name, *args, indices=None, **kwargs):
+        """The reference env's methods that make sense per env: compute_reward / get_goal_tolerance / update_goal_tolerance act
+        on shared state and return one value per selected env; forward_kinematics-style calls go through the batched API."""
+        idx = self._indices(indices)
+        out = getattr(self, name)(*args, **kwargs)
+        return [out for _ in idx]
 
     def render(self, mode='empty', **kwargs):
         return None

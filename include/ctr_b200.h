@@ -190,6 +190,13 @@ int ctr_work_counters(ctr_handle *h, double out4_host[4], void *stream);
  * (model.py:69 / :152-153), goal samplings stuck after 1001 draws (obs.py:204-205), env-steps whose action was NaN or
  * outside the action Box (ctr_reach_env.py:131-132), 0. */
 int ctr_fault_counters(ctr_handle *h, double out4_host[4], void *stream);
+/* Read-only view of the step path's internal scheduling state, for invariant tests (compute-sanitizer is not available on
+ * the build pool): slot -> env permutation (i32 [N]), per-window arrival counters (i32), refill-queue counters
+ * (i32 [6]: count[3], cursor[3]) and lists (i32 [capacity]), prefetch-slot episode tags (u32 [N]); CTR_DBG_STEP_INDEX
+ * returns the number of step launches so far in *count (queue roles: consume = index % 3, produce = (index + 1) % 3). */
+enum { CTR_DBG_PERM = 0, CTR_DBG_WINDOW_COUNTERS, CTR_DBG_QUEUE_COUNTERS, CTR_DBG_QUEUE_0, CTR_DBG_QUEUE_1, CTR_DBG_QUEUE_2,
+       CTR_DBG_SLOT_TAGS, CTR_DBG_STEP_INDEX };
+int ctr_debug_buffer(ctr_handle *h, int32_t which, void **dev_ptr, int64_t *count);
 
 /* Measured FMA-pipe peak of `device` in TFLOP/s (register-resident FMA chains; precision = CTR_PRECISION_*):
  * the roofline denominator of the FK kernels. */

@@ -145,3 +145,46 @@ def test_invalid_actions_are_counted_and_optionally_clipped(vec_factory):
     assert torch.equal(env.buffer('joints')[:, good], ref.buffer('joints')[:, good])     # valid actions are untouched
     env.stats_reset()
     assert env.fault_counters()['invalid_actions'] == 0
+
+
+def test_scheduling_state_invariants_after_heavy_resets(vec_factory):
+    """compute-sanitizer is closed on the build pool, so the lock-free bookkeeping of k_step is checked through its invariants
+    after many steps in which most envs finish (4-step episodes, wide tolerance): the slot -> env map is a permutation inside
+    every 640-slot window, every window's arrival counter is back at 0, the refill queues hold valid, distinct env ids within
+    capacity, every prefetch slot is either ready for the env's next episode or queued for a refill, and no fault was counted."""
+    n = 5000                                                  # 7 full windows + a ragged one
+    env = vec_factory(n, seed=17, max_steps_per_episode=4)
+    env.goal_tolerance.current_tol = 0.05
+    env.reset()
+    lim = torch.tensor(env.action_limits, device='cuda')
+    g = torch.Generator(device='cuda')
+    g.manual_seed(3)
+    for step in range(25):
+        env.step(((torch.rand((n, 6), device='cuda', generator=g) * 2 - 1) * lim).contiguous())
+        if step % 6 == 5:
+            mask = torch.zeros(n, dtype=torch.uint8, device='cuda')
+            mask[step::11] = 1
+            env.reset(mask=mask)                              # explicit resets interleaved with the prefetch route
+    torch.cuda.synchronize()
+    perm = env.debug_buffer(0).cpu().numpy()
+    for lo in range(0, n, 640):
+        hi = min(lo + 640, n)
+        assert np.array_equal(np.sort(perm[lo:hi]), np.arange(lo, hi)), "window %d is not a permutation" % (lo // 640)
+    assert int(env.debug_buffer(1).abs().sum()) == 0          # arrival counters reset themselves
+    ctr = env.debug_buffer(2).cpu().numpy()
+    idx = env.debug_buffer(7)
+    cap = env.debug_buffer(3).numel()
+    consume = idx % 3                                         # the queue the NEXT launch drains = produced by the last one
+    cnt = int(ctr[consume])
+    assert 0 < cnt <= cap
+    q = env.debug_buffer(3 + consume).cpu().numpy()[:cnt]
+    assert q.min() >= 0 and q.max() < n and np.unique(q).size == q.size
+    tags = env.debug_buffer(6).cpu().numpy()
+    ep = env.buffer('episode').cpu().numpy().astype(np.int64)
+    # a slot is tagged with the episode it was drawn for: ep + 1 (ready for the next reset), ep (just consumed: its refill
+    # must be waiting in the queue the next launch drains) or 0 (invalidated)
+    assert np.all((tags == 0) | (tags == ep) | (tags == ep + 1))
+    assert np.isin(np.nonzero(tags != ep + 1)[0], q).all()
+    assert (tags == ep + 1).mean() > 0.5                      # most slots are filled ahead of time
+    st = env.stats(reduce=False)
+    assert st['resets'] > 5 * n and env.fault_counters() == {'fk_failed': 0.0, 'goal_stuck': 0.0, 'invalid_actions': 0.0}

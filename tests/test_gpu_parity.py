@@ -565,6 +565,42 @@ def test_single_env_facade_matches_oracle_episode(oracle_py):
             env.close()
 
 
+def test_facade_backbone_attributes_and_vec_get_attr(oracle_c, tube_constants, vec_factory):
+    """model.r / r1 / r2 / r3 (model.py:66-68, what render('live') and src/utils.py:52-54 read) on the single-env facade; SB-style
+    get_attr / env_method with indices on the batched env."""
+    import ctr_reach_envs
+    from ctr_reach_envs.envs import CtrReachEnv
+    env = CtrReachEnv(**ctr_reach_envs.default_kwargs())
+    try:
+        env.reset()
+        env.step(env.action_space.sample())
+        q = env.trig_obj.joints.astype(np.float64)
+        r_ref, tip_idx = oracle_c.fk_shape(tube_constants[0], q)
+        assert env.model.r.shape == r_ref.shape and np.abs(env.model.r - r_ref).max() < 1e-10
+        t0, t1, t2 = (int(v) for v in tip_idx)
+        for got, want in ((env.model.r1, r_ref[t1:t0 + 1]), (env.model.r2, r_ref[t2:t1 + 1]), (env.model.r3, r_ref[:t2 + 1])):
+            assert got.shape == want.shape and np.abs(got - want).max() < 1e-10
+        live = env.render(mode='live')
+        assert set(live) == {'t', 'achieved_goal', 'desired_goal', 'r1', 'r2', 'r3'} and live['t'] == 1
+        assert np.abs(live['r1'][-1] - live['achieved_goal']).max() < 1e-10           # tube 1 ends at the tip
+        assert env.render() is None
+        tip = env.model.forward_kinematics(np.array([-0.1, -0.05, -0.02, 0.3, -0.2, 0.1]), 0)   # a direct call moves `r` with it
+        assert np.abs(env.model.r[-1] - tip).max() < 1e-10
+    finally:
+        with pytest.raises(SystemExit):
+            env.close()
+    v = vec_factory(64, select_systems=[0, 1, 2, 3], seed=5)
+    v.reset()
+    torch.cuda.synchronize()
+    sysid = v.buffer('system').cpu().numpy()
+    assert v.get_attr('system') == sysid.tolist()
+    assert v.get_attr('system', indices=[3, 7]) == [int(sysid[3]), int(sysid[7])] and v.get_attr('t', indices=5) == [0]
+    g = v.get_attr('desired_goal', indices=[1, 2])
+    assert len(g) == 2 and np.array_equal(g[1], v.buffer('desired_goal')[:, 2].cpu().numpy())
+    assert len(v.get_attr('action_space', indices=[0, 1, 2])) == 3
+    assert v.env_method('get_goal_tolerance', indices=[0, 1]) == [v.get_goal_tolerance()] * 2
+
+
 def test_host_step_entry_point_matches_device_path(vec_factory, monkeypatch):
     from ctr_reach_envs import _lib
     n = 2048
