@@ -1,0 +1,488 @@
+// ctr_bvp.cuh -- the reference's full concentric-tube model with tip load as a second kinematics back-end (SURVEY.md 8(f)
+// row 4), included by ctr_kernels.cu.
+//
+// Reference: envs/CTR_Python/CTR_Model.py -- ode_eq :56-128 (20 states: u1x u1y | u1z u2z u3z | alpha_1..3 relative to tube 1 |
+// r | R), ode_solver :130-236 (one shooting pass: per section solve_ivp(method='RK23', max_step=Tol), moment continuity at
+// the section boundaries :186-226, the 5 residuals :228-235), jac :251-262, comp :264-275, minimize :277-299.  The
+// integrator is scipy's RK23 (Bogacki-Shampine 3(2), rk.py / common.py) restated here like RK45 is in ctr_device.cuh.
+//
+// One thread per pass: this is the analysis / controller path (a Jacobian is 7 passes, a compliance matrix 4, a shooting
+// iteration 6), not the env step; its 20-dim state with four stage vectors lives in local memory.
+// Entries the reference leaves unassigned (np.empty, :63: twist derivatives of a tube absent on the section) are 0 here;
+// that is also what the golden vectors pin (oracle/ref_loader.py: _BvpLoader, oracle/make_golden_bvp.py).
+#pragma once
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+namespace ctr {
+
+constexpr int NB = 20;
+
+struct BvpSection {
+    double ei[3], gj[3], ux[3], uy[3];
+};
+
+// Segment.py:6-61 for one thread: end abscissae S[m] and the presence / curvature pattern of every kept section
+// (same arithmetic as build_sections: IEEE float64 in source order, no contraction)
+__device__ inline int bvp_sections(const double* L, const double* Lc, const double* beta, double* S, int* pat) {
+    double p[10], dtip[3], dc[3];
+    p[0] = 0.0;
+    for (int i = 0; i < 3; ++i) {
+        dtip[i] = __dadd_rn(L[i], beta[i]);
+        dc[i] = __dsub_rn(dtip[i], Lc[i]);
+        p[1 + i] = beta[i];
+        p[4 + i] = dc[i];
+        p[7 + i] = dtip[i];
+    }
+    for (int i = 1; i < 10; ++i) {                      // insertion sort (np.sort; tie order is irrelevant)
+        const double v = p[i];
+        int k = i - 1;
+        while (k >= 0 && p[k] > v) {
+            p[k + 1] = p[k];
+            --k;
+        }
+        p[k + 1] = v;
+    }
+    const double bmin = fmin(fmin(beta[0], beta[1]), beta[2]);
+    double cum = 0.0;
+    int m = 0;
+    for (int k = 0; k < 9; ++k) {
+        const double lo = p[k], hi = p[k + 1];
+        const double len = __dmul_rn(1e-5, floor(__dmul_rn(1e5, __dsub_rn(hi, lo))));   // Segment.py:16
+        if (len == 0.0) continue;
+        cum = __dadd_rn(cum, len);
+        const double s = __dadd_rn(cum, bmin);
+        if (!(s > 0.0)) continue;
+        int pt = 0;
+        for (int i = 0; i < 3; ++i) {
+            const bool present = (beta[i] <= lo) && (hi <= dtip[i]);
+            const bool curved = present && (dc[i] <= lo);
+            pt |= (present ? 1 : 0) << i;
+            pt |= (curved ? 8 : 0) << i;
+        }
+        S[m] = s;
+        pat[m] = pt;
+        m += 1;
+    }
+    return m;
+}
+
+__device__ inline void bvp_section_consts(const double* C /* L Lc EI GJ Ux Uy x3 */, int pat, BvpSection& c) {
+    for (int i = 0; i < 3; ++i) {
+        const bool present = (pat >> i) & 1, curved = (pat >> (3 + i)) & 1;
+        c.ei[i] = present ? C[6 + i] : 0.0;
+        c.gj[i] = present ? C[9 + i] : 0.0;
+        c.ux[i] = curved ? C[12 + i] : 0.0;
+        c.uy[i] = curved ? C[15 + i] : 0.0;
+    }
+}
+
+// CTR_Model.py:56-128
+__device__ inline void bvp_rhs(const BvpSection& c, const double* f, const double* y, double* d) {
+    double u[9], ca[3], sa[3];
+    ca[0] = 1.0;                                        // alpha_1 (relative to tube 1) stays 0: its derivative is u1z - u1z
+    sa[0] = 0.0;
+    sincos(y[6], &sa[1], &ca[1]);
+    sincos(y[7], &sa[2], &ca[2]);
+    if (y[5] != 0.0) sincos(y[5], &sa[0], &ca[0]);
+    u[0] = y[0];
+    u[1] = y[1];
+    u[2] = y[2];
+    for (int i = 1; i < 3; ++i) {                       // u_i = Rz(alpha_i)^T u_1 in xy, own twist (:64-73)
+        u[3 * i + 0] = ca[i] * y[0] + sa[i] * y[1];
+        u[3 * i + 1] = -sa[i] * y[0] + ca[i] * y[1];
+        u[3 * i + 2] = y[2 + i];
+    }
+    for (int i = 0; i < 3; ++i) {                       // :76-82
+        if (c.gj[i] != 0.0) {
+            d[2 + i] = (c.ei[i] / c.gj[i]) * (u[3 * i] * c.uy[i] - u[3 * i + 1] * c.ux[i]);
+            d[5 + i] = y[2 + i] - y[2];
+        } else {
+            d[2 + i] = 0.0;
+            d[5 + i] = 0.0;
+        }
+    }
+    double du0 = 0.0, du1 = 0.0, sei = 0.0;
+    for (int i = 0; i < 3; ++i) {                       // :84-112
+        const double ei = c.ei[i], gj = c.gj[i], uz = u[3 * i + 2], ux = u[3 * i], uyy = u[3 * i + 1];
+        sei += ei;
+        du0 += d[5 + i] * ei * y[1] + c.uy[i] * ei * uz * ca[i] + c.ux[i] * ei * uz * sa[i] - ei * uyy * uz * ca[i] +
+               gj * uyy * uz * ca[i] - ei * ux * uz * sa[i] + gj * ux * uz * sa[i];
+        du1 += -d[5 + i] * ei * y[0] + c.uy[i] * ei * uz * sa[i] - c.ux[i] * ei * uz * ca[i] + ei * ux * uz * ca[i] -
+               gj * ux * uz * ca[i] - ei * uyy * uz * sa[i] + gj * uyy * uz * sa[i];
+    }
+    const double* R = y + 11;
+    const double g0 = R[0] * f[0] + R[3] * f[1] + R[6] * f[2];      // R^T f
+    const double g1 = R[1] * f[0] + R[4] * f[1] + R[7] * f[2];
+    d[0] = -du0 / sei + g1 / sei;                                    // :114-118
+    d[1] = -du1 / sei - g0 / sei;
+    d[8] = R[2];
+    d[9] = R[5];
+    d[10] = R[8];
+    for (int r = 0; r < 3; ++r) {                                    // R' = R u_hat(u_1)
+        const double a = R[3 * r], b = R[3 * r + 1], cc = R[3 * r + 2];
+        d[11 + 3 * r + 0] = b * y[2] - cc * y[1];
+        d[11 + 3 * r + 1] = cc * y[0] - a * y[2];
+        d[11 + 3 * r + 2] = a * y[1] - b * y[0];
+    }
+}
+
+__device__ inline double bvp_rms(const double* x, const double* scale) {
+    double s = 0.0;
+    for (int i = 0; i < NB; ++i) {
+        const double q = x[i] / scale[i];
+        s += q * q;
+    }
+    return sqrt(s / NB);
+}
+
+struct BvpTipTwist {    // u_z of tubes 2, 3 at the stored point nearest their tips (:231-235, first minimum)
+    double best[2], uz[2];
+};
+__device__ inline void bvp_tip_note(BvpTipTwist& tz, const double* dtip, double t, const double* y) {
+    for (int i = 1; i < 3; ++i) {
+        const double dist = fabs(t - dtip[i]);
+        if (dist < tz.best[i - 1]) {
+            tz.best[i - 1] = dist;
+            tz.uz[i - 1] = y[2 + i];
+        }
+    }
+}
+
+// solve_ivp(fun, [t0, tf], y, method='RK23', max_step): y advanced in place; accepted steps, or -1 (step too small / NaN)
+__device__ inline int bvp_rk23_section(const BvpSection& c, const double* f3, double t0, double tf, double* y, double rtol,
+                                       double atol, double max_step, BvpTipTwist& tz, const double* dtip) {
+    const double A21 = 0.5, A32 = 0.75, B1 = 2.0 / 9, B2 = 1.0 / 3, B3 = 4.0 / 9, E1 = 5.0 / 72, E2 = -1.0 / 12, E3 = -1.0 / 9,
+                 E4 = 1.0 / 8;
+    double f[NB], k2[NB], k3[NB], k4[NB], yn[NB], tmp[NB];
+    double t = t0;
+    int steps = 0;
+    bvp_rhs(c, f3, y, f);
+    bvp_tip_note(tz, dtip, t, y);
+    double h_abs;
+    {   // common.py select_initial_step, error-estimator order 2
+        const double interval = fabs(tf - t0);
+        if (interval == 0.0) return 0;
+        for (int i = 0; i < NB; ++i) tmp[i] = atol + fabs(y[i]) * rtol;          // scale
+        const double d0 = bvp_rms(y, tmp), d1 = bvp_rms(f, tmp);
+        double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
+        h0 = fmin(h0, interval);
+        for (int i = 0; i < NB; ++i) yn[i] = y[i] + h0 * f[i];
+        bvp_rhs(c, f3, yn, k2);
+        for (int i = 0; i < NB; ++i) k2[i] = k2[i] - f[i];
+        const double d2 = bvp_rms(k2, tmp) / h0;
+        const double h1 = (d1 <= 1e-15 && d2 <= 1e-15) ? fmax(1e-6, h0 * 1e-3) : pow(0.01 / fmax(d1, d2), 1.0 / 3.0);
+        h_abs = fmin(fmin(100 * h0, h1), fmin(interval, max_step));
+    }
+    while (t != tf) {                                                 // rk.py _step_impl
+        const double min_step = 10 * fabs(nextafter(t, CUDART_INF) - t);
+        if (h_abs > max_step) h_abs = max_step;
+        else if (h_abs < min_step) h_abs = min_step;
+        bool rejected = false;
+        for (;;) {
+            if (h_abs < min_step) return -1;
+            double t_new = t + h_abs;
+            if (t_new - tf > 0) t_new = tf;
+            const double h = t_new - t;
+            h_abs = fabs(h);
+            for (int i = 0; i < NB; ++i) tmp[i] = y[i] + (f[i] * A21) * h;
+            bvp_rhs(c, f3, tmp, k2);
+            for (int i = 0; i < NB; ++i) tmp[i] = y[i] + (f[i] * 0.0 + k2[i] * A32) * h;
+            bvp_rhs(c, f3, tmp, k3);
+            for (int i = 0; i < NB; ++i) yn[i] = y[i] + h * (f[i] * B1 + k2[i] * B2 + k3[i] * B3);
+            bvp_rhs(c, f3, yn, k4);
+            double s = 0.0;
+            for (int i = 0; i < NB; ++i) {
+                const double sc = atol + fmax(fabs(y[i]), fabs(yn[i])) * rtol;
+                const double e = (f[i] * E1 + k2[i] * E2 + k3[i] * E3 + k4[i] * E4) * h / sc;
+                s += e * e;
+            }
+            const double err = sqrt(s / NB);
+            if (err < 1) {
+                double factor = (err == 0) ? 10.0 : fmin(10.0, 0.9 * pow(err, -1.0 / 3.0));
+                if (rejected) factor = fmin(1.0, factor);
+                h_abs *= factor;
+                t = t_new;
+                for (int i = 0; i < NB; ++i) {
+                    y[i] = yn[i];
+                    f[i] = k4[i];
+                }
+                steps += 1;
+                bvp_tip_note(tz, dtip, t, y);
+                break;
+            }
+            if (!(err == err)) return -1;
+            h_abs *= fmax(0.2, 0.9 * pow(err, -1.0 / 3.0));
+            rejected = true;
+        }
+        if (steps > 100000) return -1;
+    }
+    return steps;
+}
+
+// CTR_Model.ode_solver(u_init), method 1.  C: the 18 tube constants; q: beta[3], alpha[3] (= q + q_0); f: tip force; u: u_init.
+// y_out[20]: final state; cost[5]; returns accepted steps or -1.
+__device__ inline int bvp_pass(const double* C, const double* q, const double* f, const double* u, double max_step, double rtol,
+                               double atol, double* y, double* cost) {
+    double S[9];
+    int pat[9];
+    const int m = bvp_sections(C, C + 3, q, S, pat);
+    for (int i = 0; i < NB; ++i) y[i] = 0.0;
+    for (int i = 0; i < 5; ++i) y[i] = u[i];
+    const double a1 = q[3];
+    y[6] = q[4] - a1;                                                // :31: twist angles relative to tube 1
+    y[7] = q[5] - a1;
+    double s1, c1;
+    sincos(a1, &s1, &c1);
+    y[11] = c1;
+    y[12] = -s1;
+    y[14] = s1;
+    y[15] = c1;
+    y[19] = 1.0;
+    double dtip[3];
+    for (int i = 0; i < 3; ++i) dtip[i] = C[i] + q[i];
+    BvpTipTwist tz;
+    tz.best[0] = tz.best[1] = CUDART_INF;
+    tz.uz[0] = tz.uz[1] = 0.0;
+    int total = 0;
+    double prev = 0.0;
+    BvpSection c, cn;
+    if (m > 0) bvp_section_consts(C, pat[0], c);
+    for (int seg = 0; seg < m; ++seg) {
+        const int st = bvp_rk23_section(c, f, prev, S[seg], y, rtol, atol, max_step, tz, dtip);
+        if (st < 0) return -1;
+        total += st;
+        prev = S[seg];
+        if (seg < m - 1) {                                           // :186-226: moment continuity
+            bvp_section_consts(C, pat[seg + 1], cn);
+            double sx = 0.0, sy = 0.0, sein = 0.0;
+            for (int i = 0; i < 3; ++i) {
+                double ct = 1.0, st_ = 0.0;
+                if (i > 0) sincos(y[5 + i], &st_, &ct);
+                const double uix = ct * y[0] + st_ * y[1], uiy = -st_ * y[0] + ct * y[1];
+                const double vx = c.ei[i] * (uix - c.ux[i]) + cn.ei[i] * cn.ux[i];
+                const double vy = c.ei[i] * (uiy - c.uy[i]) + cn.ei[i] * cn.uy[i];
+                sx += ct * vx - st_ * vy;
+                sy += st_ * vx + ct * vy;
+                sein += cn.ei[i];
+            }
+            y[0] = sx / sein;
+            y[1] = sy / sein;
+            c = cn;
+        }
+    }
+    cost[0] = y[0] - c.ux[0];                                        // :228-235
+    cost[1] = y[1] - c.uy[0];
+    cost[2] = y[2];
+    cost[3] = tz.uz[0];
+    cost[4] = tz.uz[1];
+    return total;
+}
+
+// Launch shape: problem p = variant * n + i.  variant 0: the configuration as given; variants 1..6 (mode bit 0): joint
+// variant - 1 advanced by eps_q exactly as CTR_Model.jac's loop leaves q (:257-261: earlier joints went + eps - eps);
+// the next 3 variants (mode bit 1): tip-force component advanced by eps_f as comp does (:270-274); the next 5 (mode
+// bit 2): u_init component advanced by eps_u (shooting Jacobian).  Outputs are [rows][variants * n].
+struct BvpArgs {
+    const SysConst* sys;
+    int n_systems;
+    const double* q;        // f64 [6][n]
+    const double* f;        // f64 [3][n] or null (no tip load)
+    const double* u;        // f64 [5][n] or null (zeros)
+    const int32_t* system;  // i32 [n] or null
+    const double* params;   // f64 [18][n] per-config tube constants or null
+    int64_t n;
+    int32_t mode;
+    double eps_q, eps_f, eps_u, max_step, rtol, atol;
+    double* tip;            // f64 [3][V n]
+    double* R;              // f64 [9][V n] or null
+    double* cost;           // f64 [5][V n] or null
+    int32_t* steps;         // i32 [V n] or null
+    double* fault;          // stats slot for failed passes or null
+};
+
+__device__ __host__ inline int bvp_variants(int mode) { return 1 + ((mode & 1) ? 6 : 0) + ((mode & 2) ? 3 : 0) + ((mode & 4) ? 5 : 0); }
+
+__global__ void __launch_bounds__(64) k_bvp_pass(const BvpArgs a) {
+    const int V = bvp_variants(a.mode);
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= (int64_t)V * a.n) return;
+    const int v = (int)(p / a.n);
+    const int64_t i = p - (int64_t)v * a.n;
+    double C[18], q[6], f[3] = {0.0, 0.0, 0.0}, u[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+    if (a.params) {
+        for (int k = 0; k < 18; ++k) C[k] = a.params[(int64_t)k * a.n + i];
+    } else {
+        int s = a.system ? a.system[i] : 0;
+        s = min(max(s, 0), a.n_systems - 1);
+        const SysConst& sc = a.sys[s];
+        for (int k = 0; k < 3; ++k) {
+            C[k] = sc.L[k];
+            C[3 + k] = sc.Lc[k];
+            C[6 + k] = sc.EI[k];
+            C[9 + k] = sc.GJ[k];
+            C[12 + k] = sc.Ux[k];
+            C[15 + k] = sc.Uy[k];
+        }
+    }
+    for (int k = 0; k < 6; ++k) q[k] = a.q[(int64_t)k * a.n + i];
+    if (a.f)
+        for (int k = 0; k < 3; ++k) f[k] = a.f[(int64_t)k * a.n + i];
+    if (a.u)
+        for (int k = 0; k < 5; ++k) u[k] = a.u[(int64_t)k * a.n + i];
+    int w = v - 1;                                       // which perturbation this variant is
+    if (v > 0 && (a.mode & 1)) {
+        if (w < 6) {
+            for (int k = 0; k < w; ++k) q[k] = __dsub_rn(__dadd_rn(q[k], a.eps_q), a.eps_q);
+            q[w] = __dadd_rn(q[w], a.eps_q);
+            w = -1;
+        } else {
+            w -= 6;
+        }
+    }
+    if (w >= 0 && (a.mode & 2)) {
+        if (w < 3) {
+            for (int k = 0; k < w; ++k) f[k] = __dsub_rn(__dadd_rn(f[k], a.eps_f), a.eps_f);
+            f[w] = __dadd_rn(f[w], a.eps_f);
+            w = -1;
+        } else {
+            w -= 3;
+        }
+    }
+    if (w >= 0 && (a.mode & 4) && w < 5) u[w] = __dadd_rn(u[w], a.eps_u);
+    double y[NB], cost[5];
+    const int st = bvp_pass(C, q, f, u, a.max_step, a.rtol, a.atol, y, cost);
+    const int64_t M = (int64_t)V * a.n;
+    const double bad = __longlong_as_double(0x7ff8000000000000LL);
+    for (int k = 0; k < 3; ++k) a.tip[(int64_t)k * M + p] = (st < 0) ? bad : y[8 + k];
+    if (a.R)
+        for (int k = 0; k < 9; ++k) a.R[(int64_t)k * M + p] = (st < 0) ? bad : y[11 + k];
+    if (a.cost)
+        for (int k = 0; k < 5; ++k) a.cost[(int64_t)k * M + p] = (st < 0) ? bad : cost[k];
+    if (a.steps) a.steps[p] = st;
+    if (st < 0 && a.fault) atomicAdd(a.fault, 1.0);
+}
+
+// Forward differences over the variant block: J f64 [18][n] (3 x 6 row-major), Cm f64 [9][n] (3 x 3), tip0 f64 [3][n]
+__global__ void k_bvp_fd(const double* __restrict__ tips, int64_t n, int mode, double eps_q, double eps_f, double* __restrict__ J,
+                         double* __restrict__ Cm, double* __restrict__ tip0) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int V = bvp_variants(mode);
+    const int64_t M = (int64_t)V * n;
+    double P[3];
+    for (int r = 0; r < 3; ++r) {
+        P[r] = tips[(int64_t)r * M + i];
+        if (tip0) tip0[(int64_t)r * n + i] = P[r];
+    }
+    int base = 1;
+    if (mode & 1) {
+        if (J)
+            for (int c = 0; c < 6; ++c)
+                for (int r = 0; r < 3; ++r)
+                    J[(int64_t)(r * 6 + c) * n + i] = __ddiv_rn(__dsub_rn(tips[(int64_t)r * M + (int64_t)(base + c) * n + i], P[r]), eps_q);
+        base += 6;
+    }
+    if ((mode & 2) && Cm)
+        for (int c = 0; c < 3; ++c)
+            for (int r = 0; r < 3; ++r)
+                Cm[(int64_t)(r * 3 + c) * n + i] = __ddiv_rn(__dsub_rn(tips[(int64_t)r * M + (int64_t)(base + c) * n + i], P[r]), eps_f);
+}
+
+// One Newton step of the shooting problem cost(u) = 0 on the 6-variant block (base + 5 perturbed u): solves the 5 x 5
+// forward-difference system by Gaussian elimination with partial pivoting, u += damping * du for the configurations whose
+// residual max-norm is still above f_tol (scipy.optimize.anderson's default norm and the reference's f_tol, :296).
+__global__ void k_bvp_newton(const double* __restrict__ cost, int64_t n, double eps_u, double f_tol, double damping,
+                             double* __restrict__ u, double* __restrict__ res, int32_t* __restrict__ iters,
+                             uint8_t* __restrict__ frozen, int32_t* __restrict__ active) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || frozen[i]) return;
+    const int64_t M = 6 * n;
+    double c0[5], A[5][6];
+    double nrm = 0.0;
+    bool bad = false;
+    for (int r = 0; r < 5; ++r) {
+        c0[r] = cost[(int64_t)r * M + i];
+        bad |= !(c0[r] == c0[r]);
+        nrm = fmax(nrm, fabs(c0[r]));
+    }
+    res[i] = bad ? CUDART_NAN : nrm;
+    if (bad || nrm < f_tol) {
+        frozen[i] = 1;
+        return;
+    }
+    for (int r = 0; r < 5; ++r) {
+        for (int c = 0; c < 5; ++c) A[r][c] = (cost[(int64_t)r * M + (int64_t)(1 + c) * n + i] - c0[r]) / eps_u;
+        A[r][5] = -c0[r];
+    }
+    for (int k = 0; k < 5; ++k) {
+        int piv = k;
+        for (int r = k + 1; r < 5; ++r)
+            if (fabs(A[r][k]) > fabs(A[piv][k])) piv = r;
+        for (int c = 0; c < 6; ++c) {
+            const double t = A[k][c];
+            A[k][c] = A[piv][c];
+            A[piv][c] = t;
+        }
+        const double d = A[k][k];
+        if (!(fabs(d) > 1e-300)) {
+            frozen[i] = 1;                                // singular Jacobian: give up on this configuration (res says how far)
+            return;
+        }
+        for (int r = k + 1; r < 5; ++r) {
+            const double m = A[r][k] / d;
+            for (int c = k; c < 6; ++c) A[r][c] -= m * A[k][c];
+        }
+    }
+    double du[5];
+    for (int k = 4; k >= 0; --k) {
+        double s = A[k][5];
+        for (int c = k + 1; c < 5; ++c) s -= A[k][c] * du[c];
+        du[k] = s / A[k][k];
+    }
+    for (int k = 0; k < 5; ++k) u[(int64_t)k * n + i] += damping * du[k];
+    iters[i] += 1;
+    atomicAdd(active, 1);
+}
+
+// initial guess of CTR_Model.minimize (:279-294): u1_xy from the precurvatures of the first section, zero twist curvature
+__global__ void k_bvp_guess(const BvpArgs a, double* __restrict__ u) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    double C[18], q[6];
+    if (a.params) {
+        for (int k = 0; k < 18; ++k) C[k] = a.params[(int64_t)k * a.n + i];
+    } else {
+        int s = a.system ? a.system[i] : 0;
+        s = min(max(s, 0), a.n_systems - 1);
+        const SysConst& sc = a.sys[s];
+        for (int k = 0; k < 3; ++k) {
+            C[k] = sc.L[k];
+            C[3 + k] = sc.Lc[k];
+            C[6 + k] = sc.EI[k];
+            C[9 + k] = sc.GJ[k];
+            C[12 + k] = sc.Ux[k];
+            C[15 + k] = sc.Uy[k];
+        }
+    }
+    for (int k = 0; k < 6; ++k) q[k] = a.q[(int64_t)k * a.n + i];
+    double S[9];
+    int pat[9];
+    const int m = bvp_sections(C, C + 3, q, S, pat);
+    BvpSection c;
+    bvp_section_consts(C, m > 0 ? pat[0] : 0, c);
+    double sx = 0.0, sy = 0.0, sei = 0.0;
+    for (int k = 0; k < 3; ++k) {
+        const double al = (k == 0) ? 0.0 : q[3 + k] - q[3];
+        const double ct = cos(-al), st = sin(-al);
+        sx += c.ei[k] * c.ux[k] * ct + c.ei[k] * c.uy[k] * st;
+        sy += -c.ei[k] * c.ux[k] * st + c.ei[k] * c.uy[k] * ct;
+        sei += c.ei[k];
+    }
+    u[i] = sx / sei;
+    u[a.n + i] = sy / sei;
+    for (int k = 2; k < 5; ++k) u[(int64_t)k * a.n + i] = 0.0;
+}
+
+}  // namespace ctr

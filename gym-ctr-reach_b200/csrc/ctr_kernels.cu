@@ -22,6 +22,7 @@
 #include "ctr_device.cuh"
 #include "ctr_her.cuh"
 #include "ctr_ik.cuh"
+#include "ctr_bvp.cuh"
 
 using namespace ctr;
 
@@ -934,6 +935,8 @@ struct ctr_handle {
     float* stage_action;
     int64_t stage_fk_cap;
     void* stage_fk_dev;
+    size_t bvp_cap;            // ctr_bvp_* scratch (bytes)
+    void* bvp_dev;
     int64_t ik_cap;            // ctr_jacobian / ctr_ik_dls scratch: joints f64 [6][7n] | tips f64 [3][7n] | system i32 [7n] | frozen u8 [n] | active i32
     void* ik_dev;
 };
@@ -1128,6 +1131,8 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     h->stage_fk_dev = nullptr;
     h->ik_cap = 0;
     h->ik_dev = nullptr;
+    h->bvp_cap = 0;
+    h->bvp_dev = nullptr;
     cudaDeviceProp prop;
     CTR_CUDA(cudaGetDeviceProperties(&prop, device));
     h->sm_count = prop.multiProcessorCount;
@@ -1247,6 +1252,7 @@ int ctr_destroy(ctr_handle* h) {
     if (h->stage_action) cudaFree(h->stage_action);      // device staging of ctr_step_host (cudaMalloc, step_host_impl)
     if (h->stage_fk_dev) cudaFree(h->stage_fk_dev);
     if (h->ik_dev) cudaFree(h->ik_dev);
+    if (h->bvp_dev) cudaFree(h->bvp_dev);
     if (h->stream) cudaStreamDestroy(h->stream);
     for (int k = 1; k <= N_COMPUTE_STREAMS; ++k) {
         if (h->streams[k]) cudaStreamDestroy(h->streams[k]);
@@ -1964,6 +1970,172 @@ int ctr_ik_dls(ctr_handle* h, const double* target_dev, double* joints_dev, cons
             CTR_CUDA(cudaMemcpyAsync(&active, sc.active, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
             CTR_CUDA(cudaStreamSynchronize(st));
             if (active == 0) break;
+        }
+    }
+    CTR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+
+// ---- BVP back-end (csrc/ctr_bvp.cuh; CTR_Python/CTR_Model.py) --------------------------------------------------------
+static int bvp_scratch(ctr_handle* h, size_t bytes, char** out) {
+    if (h->bvp_cap < bytes) {
+        if (h->bvp_dev) CTR_CUDA(cudaFree(h->bvp_dev));
+        h->bvp_dev = nullptr;
+        h->bvp_cap = 0;
+        CTR_CUDA(cudaMalloc(&h->bvp_dev, bytes));
+        h->bvp_cap = bytes;
+    }
+    *out = (char*)h->bvp_dev;
+    return 0;
+}
+static BvpArgs bvp_args(ctr_handle* h, const double* q, const double* f, const double* u, const int32_t* system,
+                        const double* params, int64_t n, int32_t mode, double max_step) {
+    BvpArgs a;
+    memset(&a, 0, sizeof a);
+    a.sys = h->sys_dev;
+    a.n_systems = h->cfg.n_systems;
+    a.q = q;
+    a.f = f;
+    a.u = u;
+    a.system = system;
+    a.params = params;
+    a.n = n;
+    a.mode = mode;
+    a.eps_q = 1e-4;                  // CTR_Model.py:17
+    a.eps_f = 0.05;                  // CTR_Model.py:270
+    a.eps_u = 1e-6;
+    a.max_step = max_step;
+    a.rtol = 1e-3;                   // solve_ivp defaults (no tolerances passed, CTR_Model.py:164-167)
+    a.atol = 1e-6;
+    a.fault = h->p.stats + ST_FK_FAILED;
+    return a;
+}
+static int bvp_launch(ctr_handle* h, const BvpArgs& a, cudaStream_t st) {
+    const int64_t total = (int64_t)bvp_variants(a.mode) * a.n;
+    k_bvp_pass<<<(int)((total + 63) / 64), 64, 0, st>>>(a);
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int ctr_bvp_pass(ctr_handle* h, const double* q_dev, const double* f_dev, const double* u_dev, const int32_t* system_dev,
+                 const double* params_dev, int64_t n, double max_step, double* tip_dev, double* R_dev, double* cost_dev,
+                 int32_t* steps_dev, void* stream) {
+    if (!h || !q_dev || !tip_dev) CTR_FAIL("null argument");
+    if (!(max_step > 0.0)) CTR_FAIL("max_step must be > 0");
+    if (n <= 0) return 0;
+    CTR_CUDA(cudaSetDevice(h->device));
+    BvpArgs a = bvp_args(h, q_dev, f_dev, u_dev, system_dev, params_dev, n, 0, max_step);
+    a.tip = tip_dev;
+    a.R = R_dev;
+    a.cost = cost_dev;
+    a.steps = steps_dev;
+    return bvp_launch(h, a, (cudaStream_t)stream);
+}
+
+int ctr_bvp_jacobian(ctr_handle* h, const double* q_dev, const double* f_dev, const double* u_dev, const int32_t* system_dev,
+                     const double* params_dev, int64_t n, double max_step, double* J_dev, double* C_dev, double* tip_dev,
+                     void* stream) {
+    if (!h || !q_dev || (!J_dev && !C_dev)) CTR_FAIL("null argument");
+    if (!(max_step > 0.0)) CTR_FAIL("max_step must be > 0");
+    if (n <= 0) return 0;
+    CTR_CUDA(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int mode = (J_dev ? 1 : 0) | (C_dev ? 2 : 0);
+    char* base = nullptr;
+    int rc = bvp_scratch(h, sizeof(double) * 3 * (size_t)bvp_variants(mode) * (size_t)n, &base);
+    if (rc) return rc;
+    BvpArgs a = bvp_args(h, q_dev, f_dev, u_dev, system_dev, params_dev, n, mode, max_step);
+    a.tip = (double*)base;
+    rc = bvp_launch(h, a, st);
+    if (rc) return rc;
+    k_bvp_fd<<<(int)((n + 127) / 128), 128, 0, st>>>(a.tip, n, mode, a.eps_q, a.eps_f, J_dev, C_dev, tip_dev);
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int ctr_bvp_solve(ctr_handle* h, const double* q_dev, const double* f_dev, const int32_t* system_dev, const double* params_dev,
+                  int64_t n, double max_step, double f_tol, int32_t max_iters, double* u_dev, double* tip_dev, double* cost_dev,
+                  double* res_dev, int32_t* iters_dev, void* stream) {
+    if (!h || !q_dev || !u_dev || !res_dev || !iters_dev) CTR_FAIL("null argument");
+    if (!(max_step > 0.0) || !(f_tol > 0.0) || max_iters < 0) CTR_FAIL("bad max_step / f_tol / max_iters");
+    if (n <= 0) return 0;
+    CTR_CUDA(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    // scratch: tips f64 [3][6n] | cost f64 [5][6n] | active i32 [16] | frozen u8 [n]
+    char* base = nullptr;
+    int rc = bvp_scratch(h, (size_t)n * (6 * 8 * 8 + 1) + 64, &base);
+    if (rc) return rc;
+    double* tips = (double*)base;
+    double* cost = tips + 18 * n;
+    int32_t* active = (int32_t*)(cost + 30 * n);
+    uint8_t* frozen = (uint8_t*)(active + 16);
+    BvpArgs a = bvp_args(h, q_dev, f_dev, u_dev, system_dev, params_dev, n, 4, max_step);
+    a.tip = tips;
+    a.cost = cost;
+    k_bvp_guess<<<(int)((n + 127) / 128), 128, 0, st>>>(a, u_dev);          // CTR_Model.minimize's starting point
+    h->launches += 1;
+    CTR_CUDA(cudaMemsetAsync(frozen, 0, (size_t)n, st));
+    CTR_CUDA(cudaMemsetAsync(iters_dev, 0, sizeof(int32_t) * n, st));
+    for (int it = 0; it <= max_iters; ++it) {
+        CTR_CUDA(cudaMemsetAsync(active, 0, sizeof(int32_t), st));
+        rc = bvp_launch(h, a, st);
+        if (rc) return rc;
+        k_bvp_newton<<<(int)((n + 127) / 128), 128, 0, st>>>(cost, n, a.eps_u, it == max_iters ? (double)INFINITY : f_tol, 1.0, u_dev,
+                                                              res_dev, iters_dev, frozen, active);
+        h->launches += 1;
+        CTR_CUDA(cudaGetLastError());
+        int32_t act = 0;
+        CTR_CUDA(cudaMemcpyAsync(&act, active, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        CTR_CUDA(cudaStreamSynchronize(st));
+        if (act == 0) break;
+    }
+    if (tip_dev || cost_dev) {                                               // the pass at the solution
+        BvpArgs b = bvp_args(h, q_dev, f_dev, u_dev, system_dev, params_dev, n, 0, max_step);
+        b.tip = tip_dev ? tip_dev : tips;
+        b.cost = cost_dev;
+        rc = bvp_launch(h, b, st);
+        if (rc) return rc;
+    }
+    CTR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int ctr_bvp_ik_dls(ctr_handle* h, const double* target_dev, double* q_dev, const int32_t* system_dev, int64_t n, double lam,
+                   double tol, int32_t max_iters, double max_step, double* err_dev, int32_t* iters_dev, void* stream) {
+    if (!h || !target_dev || !q_dev || !err_dev || !iters_dev) CTR_FAIL("null argument");
+    if (!(lam >= 0.0) || max_iters < 0 || !(max_step > 0.0)) CTR_FAIL("bad lam / max_iters / max_step");
+    if (n <= 0) return 0;
+    CTR_CUDA(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    // scratch: tips f64 [3][7n] | active i32 [16] | frozen u8 [n]
+    char* base = nullptr;
+    int rc = bvp_scratch(h, (size_t)n * (21 * 8 + 1) + 64, &base);
+    if (rc) return rc;
+    double* tips = (double*)base;
+    int32_t* active = (int32_t*)(tips + 21 * n);
+    uint8_t* frozen = (uint8_t*)(active + 16);
+    CTR_CUDA(cudaMemsetAsync(frozen, 0, (size_t)n, st));
+    CTR_CUDA(cudaMemsetAsync(iters_dev, 0, sizeof(int32_t) * n, st));
+    CTR_CUDA(cudaMemsetAsync(err_dev, 0, sizeof(double) * n, st));
+    // src/jacobian_controller.py:19-53: CTR_Model(..., f = 0, q, q_0 = 0, Tol, 1).jac(u_init = 0) every iteration
+    BvpArgs a = bvp_args(h, q_dev, nullptr, nullptr, system_dev, nullptr, n, 1, max_step);
+    a.tip = tips;
+    for (int it = 0; it < max_iters; ++it) {
+        CTR_CUDA(cudaMemsetAsync(active, 0, sizeof(int32_t), st));
+        rc = bvp_launch(h, a, st);
+        if (rc) return rc;
+        k_ik_dls_update<<<(int)((n + 255) / 256), 256, 0, st>>>(tips, target_dev, n, a.eps_q, lam, tol, q_dev, err_dev, iters_dev,
+                                                               frozen, active);
+        h->launches += 1;
+        CTR_CUDA(cudaGetLastError());
+        if ((it & 3) == 3 || it == max_iters - 1) {
+            int32_t act = 0;
+            CTR_CUDA(cudaMemcpyAsync(&act, active, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+            CTR_CUDA(cudaStreamSynchronize(st));
+            if (act == 0) break;
         }
     }
     CTR_CUDA(cudaStreamSynchronize(st));

@@ -26,7 +26,8 @@ EXPORTS = ['ctr_last_error', 'ctr_abi_version', 'ctr_create', 'ctr_destroy', 'ct
            'ctr_fk_host', 'ctr_set_action', 'ctr_set_state_host', 'ctr_reset', 'ctr_step', 'ctr_step_strided',
            'ctr_step_host', 'ctr_step_host_packed', 'ctr_reset_host', 'ctr_compute_reward', 'ctr_relabel', 'ctr_stats', 'ctr_stats_reset',
            'ctr_launch_count', 'ctr_work_counters', 'ctr_fault_counters', 'ctr_debug_buffer', 'ctr_measure_fma_peak', 'ctr_her_begin', 'ctr_her_store',
-           'ctr_her_sample', 'ctr_fk_shape', 'ctr_jacobian', 'ctr_ik_dls']
+           'ctr_her_sample', 'ctr_fk_shape', 'ctr_jacobian', 'ctr_ik_dls', 'ctr_bvp_pass', 'ctr_bvp_jacobian', 'ctr_bvp_solve',
+           'ctr_bvp_ik_dls']
 
 
 class CtrConfig(ctypes.Structure):
@@ -126,6 +127,10 @@ def load():
     lib.ctr_fk_shape.argtypes = [vp, vp, vp, vp, i64, i32, vp, vp, vp, vp, vp]
     lib.ctr_jacobian.argtypes = [vp, vp, vp, i64, f64, vp, vp, vp]
     lib.ctr_ik_dls.argtypes = [vp, vp, vp, vp, i64, f64, f64, f64, i32, vp, vp, vp]
+    lib.ctr_bvp_pass.argtypes = [vp, vp, vp, vp, vp, vp, i64, f64, vp, vp, vp, vp, vp]
+    lib.ctr_bvp_jacobian.argtypes = [vp, vp, vp, vp, vp, vp, i64, f64, vp, vp, vp, vp]
+    lib.ctr_bvp_solve.argtypes = [vp, vp, vp, vp, vp, i64, f64, f64, i32, vp, vp, vp, vp, vp, vp]
+    lib.ctr_bvp_ik_dls.argtypes = [vp, vp, vp, vp, i64, f64, f64, i32, f64, vp, vp, vp]
     lib.ctr_her_begin.argtypes = [vp, ctypes.POINTER(CtrHerRing), vp]
     lib.ctr_her_store.argtypes = [vp, ctypes.POINTER(CtrHerRing), vp, i64, i64, i64, vp]
     lib.ctr_her_sample.argtypes = [vp, ctypes.POINTER(CtrHerRing), i64, i64, i32, i32, f64, ctypes.c_uint64, ctypes.c_uint64,

@@ -297,6 +297,73 @@ class CtrReachVecEnv(object):
                                        int(max_iters), _lib.ptr(err), _lib.ptr(iters), self._stream()))
         return q.t(), err, iters
 
+    # ---- BVP back-end: CTR_Python/CTR_Model.py (the reference's full model with tip load) -------------------------------
+    def _soa(self, x, rows, n=None, dtype=torch.float64):
+        if x is None:
+            return None
+        t = torch.as_tensor(x, dtype=dtype, device=self.device)
+        t = t.reshape(-1, rows) if n is None else t.expand(n, rows) if t.dim() == 2 else t.reshape(1, rows).expand(n, rows)
+        return t.t().contiguous()
+
+    def bvp_pass(self, joints, force=None, u_init=None, system=None, params=None, max_step=0.01):
+        """CTR_Model(..., f, q, 0, Tol = max_step, 1).ode_solver(u_init) batched: joints (n, 6) float64 -> dict(tip (n, 3),
+        R (n, 9), cost (n, 5), steps (n,)).  force (n, 3) or None, u_init (n, 5) or None (zeros)."""
+        q = self._soa(joints, 6)
+        n = q.shape[1]
+        f, u = self._soa(force, 3, n), self._soa(u_init, 5, n)
+        s = None if system is None else torch.as_tensor(system, dtype=torch.int32, device=self.device).expand(n).contiguous()
+        p = self._soa(params, 18, n)
+        tip = torch.empty((3, n), dtype=torch.float64, device=self.device)
+        R = torch.empty((9, n), dtype=torch.float64, device=self.device)
+        cost = torch.empty((5, n), dtype=torch.float64, device=self.device)
+        steps = torch.empty(n, dtype=torch.int32, device=self.device)
+        _lib.check(self.lib.ctr_bvp_pass(self.handle, _lib.ptr(q), _lib.ptr(f), _lib.ptr(u), _lib.ptr(s), _lib.ptr(p), n,
+                                         float(max_step), _lib.ptr(tip), _lib.ptr(R), _lib.ptr(cost), _lib.ptr(steps), self._stream()))
+        return dict(tip=tip.t(), R=R.t(), cost=cost.t(), steps=steps)
+
+    def bvp_jacobian(self, joints, force=None, u_init=None, system=None, params=None, max_step=0.01, compliance=True):
+        """CTR_Model.jac (and comp): J (n, 3, 6), C (n, 3, 3) or None, tip (n, 3)."""
+        q = self._soa(joints, 6)
+        n = q.shape[1]
+        f, u = self._soa(force, 3, n), self._soa(u_init, 5, n)
+        s = None if system is None else torch.as_tensor(system, dtype=torch.int32, device=self.device).expand(n).contiguous()
+        p = self._soa(params, 18, n)
+        J = torch.empty((18, n), dtype=torch.float64, device=self.device)
+        C = torch.empty((9, n), dtype=torch.float64, device=self.device) if compliance else None
+        tip = torch.empty((3, n), dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.ctr_bvp_jacobian(self.handle, _lib.ptr(q), _lib.ptr(f), _lib.ptr(u), _lib.ptr(s), _lib.ptr(p), n,
+                                             float(max_step), _lib.ptr(J), _lib.ptr(C), _lib.ptr(tip), self._stream()))
+        return J.t().reshape(n, 3, 6), (C.t().reshape(n, 3, 3) if compliance else None), tip.t()
+
+    def bvp_solve(self, joints, force=None, system=None, params=None, max_step=0.01, f_tol=1e-3, max_iters=40):
+        """The shooting problem of CTR_Model.minimize: dict(u (n, 5), tip (n, 3), cost (n, 5), residual (n,), iters (n,))."""
+        q = self._soa(joints, 6)
+        n = q.shape[1]
+        f = self._soa(force, 3, n)
+        s = None if system is None else torch.as_tensor(system, dtype=torch.int32, device=self.device).expand(n).contiguous()
+        p = self._soa(params, 18, n)
+        u = torch.zeros((5, n), dtype=torch.float64, device=self.device)
+        tip = torch.empty((3, n), dtype=torch.float64, device=self.device)
+        cost = torch.empty((5, n), dtype=torch.float64, device=self.device)
+        res = torch.empty(n, dtype=torch.float64, device=self.device)
+        iters = torch.empty(n, dtype=torch.int32, device=self.device)
+        _lib.check(self.lib.ctr_bvp_solve(self.handle, _lib.ptr(q), _lib.ptr(f), _lib.ptr(s), _lib.ptr(p), n, float(max_step),
+                                          float(f_tol), int(max_iters), _lib.ptr(u), _lib.ptr(tip), _lib.ptr(cost), _lib.ptr(res),
+                                          _lib.ptr(iters), self._stream()))
+        return dict(u=u.t(), tip=tip.t(), cost=cost.t(), residual=res, iters=iters)
+
+    def bvp_ik_dls(self, target, q0, system=None, lam=0.25, tol=1e-3, max_iters=500, max_step=0.01):
+        """src/jacobian_controller.py:19-53 (dls_ik_position_only) on the model it was written for: q (n, 6), err, iters."""
+        q = self._soa(q0, 6).clone()
+        n = q.shape[1]
+        tg = self._soa(target, 3, n)
+        s = None if system is None else torch.as_tensor(system, dtype=torch.int32, device=self.device).expand(n).contiguous()
+        err = torch.empty(n, dtype=torch.float64, device=self.device)
+        iters = torch.empty(n, dtype=torch.int32, device=self.device)
+        _lib.check(self.lib.ctr_bvp_ik_dls(self.handle, _lib.ptr(tg), _lib.ptr(q), _lib.ptr(s), n, float(lam), float(tol),
+                                           int(max_iters), float(max_step), _lib.ptr(err), _lib.ptr(iters), self._stream()))
+        return q.t(), err, iters
+
     def set_tube_params(self, params):
         """Per-env derived constants (N, 18) = L, Lc, EI, GJ, Ux, Uy (x3 each) or None (model.py:20-28)."""
         if params is None:

@@ -233,6 +233,34 @@ int ctr_jacobian(ctr_handle *h, const double *joints_dev, const int32_t *system_
 int ctr_ik_dls(ctr_handle *h, const double *target_dev, double *joints_dev, const int32_t *system_dev, int64_t n, double lam,
                double eps, double tol, int32_t max_iters, double *err_dev, int32_t *iters_dev, void *stream);
 
+/* ---- the reference's full model with tip load (CTR_Python/CTR_Model.py) as a second kinematics back-end
+ * State of the model: u1x u1y | u1z u2z u3z | twist angles relative to tube 1 | r | R (20 values, ode_eq :56-128), integrated
+ * section by section with scipy's RK23 and max_step (ode_solver :130-236).  All arrays are SoA f64 [rows][n].
+ *   q     [6][n]  joints = q + q_0 of the reference (beta[3], alpha[3])
+ *   f     [3][n]  tip force, NULL = no load;  u [5][n] initial curvatures u_init, NULL = zeros (what jacobian_controller.py passes)
+ *   system i32 [n] or NULL (system 0);  params [18][n] per-configuration tube constants or NULL
+ * ctr_bvp_pass      = CTR_Model.ode_solver(u_init), method 1: tip [3][n], final R [9][n] / residuals cost [5][n] (:228-235) /
+ *                     accepted RK23 steps i32 [n] optional.  A failed pass (step too small) writes NaN and counts in
+ *                     ctr_fault_counters()[0].
+ * ctr_bvp_jacobian  = CTR_Model.jac (:251-262, eps 1e-4 on q, q restored by subtraction as there) and / or CTR_Model.comp
+ *                     (:264-275, 0.05 N on f): J [18][n] (3 x 6 row-major) and / or C [9][n] (3 x 3), tip [3][n] optional.
+ * ctr_bvp_solve     = the shooting problem of CTR_Model.minimize (:277-299): starts from the same initial guess and drives the
+ *                     same 5 residuals below the same f_tol (max-norm, scipy.optimize.anderson's), by Newton steps on a
+ *                     forward-difference 5 x 5 Jacobian (6 passes per iteration) instead of Anderson mixing.  u [5][n] out,
+ *                     res [n] final residual max-norm, iters i32 [n]; tip / cost of the pass at the solution optional.  Synchronises.
+ * ctr_bvp_ik_dls    = src/jacobian_controller.py:19-53 on this model: q [6][n] in/out, target [3][n]; as ctr_ik_dls.  Synchronises. */
+int ctr_bvp_pass(ctr_handle *h, const double *q_dev, const double *f_dev, const double *u_dev, const int32_t *system_dev,
+                 const double *params_dev, int64_t n, double max_step, double *tip_dev, double *R_dev, double *cost_dev,
+                 int32_t *steps_dev, void *stream);
+int ctr_bvp_jacobian(ctr_handle *h, const double *q_dev, const double *f_dev, const double *u_dev, const int32_t *system_dev,
+                     const double *params_dev, int64_t n, double max_step, double *J_dev, double *C_dev, double *tip_dev,
+                     void *stream);
+int ctr_bvp_solve(ctr_handle *h, const double *q_dev, const double *f_dev, const int32_t *system_dev, const double *params_dev,
+                  int64_t n, double max_step, double f_tol, int32_t max_iters, double *u_dev, double *tip_dev, double *cost_dev,
+                  double *res_dev, int32_t *iters_dev, void *stream);
+int ctr_bvp_ik_dls(ctr_handle *h, const double *target_dev, double *q_dev, const int32_t *system_dev, int64_t n, double lam,
+                   double tol, int32_t max_iters, double max_step, double *err_dev, int32_t *iters_dev, void *stream);
+
 /* ---- hindsight replay on the device --------------------------------------------------------
  * Replaces what the reference delegates to stable_baselines' HER wrapper (third party, not vendored, version not
  * pinned: setup.py:5; call sites src/utils.py:5-7,27-28; settings saved_policies/.../config.yml: goal_selection_strategy

@@ -108,3 +108,31 @@ def step_batch(tc, L, joints, action, desired, t, tol, n_substeps=10, max_steps=
                                       _p(reward), _p(done), ctypes.c_int64(n), ctypes.c_int(nthreads))
     assert bad == 0
     return achieved, reward, done
+
+
+def bvp_pass(tc, q, f=None, u_init=None, max_step=0.01, rtol=1e-3, atol=1e-6):
+    """One shooting pass of the BVP model (CTR_Model.ode_solver, method 1): dict(tip[3], R[9], cost[5], y[20], steps)."""
+    out = np.zeros(38)
+    f = np.zeros(3) if f is None else np.ascontiguousarray(f, dtype=np.float64).reshape(3)
+    u = np.zeros(5) if u_init is None else np.ascontiguousarray(u_init, dtype=np.float64).reshape(5)
+    fn = lib().ctr_oracle_bvp_pass
+    fn.restype = ctypes.c_int
+    rc = fn(_p(np.ascontiguousarray(tc, dtype=np.float64)), _p(np.ascontiguousarray(q, dtype=np.float64)), _p(f), _p(u),
+            ctypes.c_double(max_step), ctypes.c_double(rtol), ctypes.c_double(atol), _p(out))
+    if rc:
+        raise RuntimeError("ctr_oracle_bvp_pass failed")
+    return dict(tip=out[:3].copy(), R=out[3:12].copy(), cost=out[12:17].copy(), y=out[17:37].copy(), steps=int(out[37]))
+
+
+def bvp_jac_comp(tc, q, f=None, u_init=None, max_step=0.01, rtol=1e-3, atol=1e-6):
+    """CTR_Model.jac / comp (forward differences over passes): J (3, 6), C (3, 3), tip (3,)."""
+    J, Cm, tip = np.zeros((3, 6)), np.zeros((3, 3)), np.zeros(3)
+    f = np.zeros(3) if f is None else np.ascontiguousarray(f, dtype=np.float64).reshape(3)
+    u = np.zeros(5) if u_init is None else np.ascontiguousarray(u_init, dtype=np.float64).reshape(5)
+    fn = lib().ctr_oracle_bvp_jac_comp
+    fn.restype = ctypes.c_int
+    rc = fn(_p(np.ascontiguousarray(tc, dtype=np.float64)), _p(np.ascontiguousarray(q, dtype=np.float64)), _p(f), _p(u),
+            ctypes.c_double(max_step), ctypes.c_double(rtol), ctypes.c_double(atol), _p(J), _p(Cm), _p(tip))
+    if rc:
+        raise RuntimeError("ctr_oracle_bvp_jac_comp failed")
+    return J, Cm, tip

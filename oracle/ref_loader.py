@@ -46,8 +46,30 @@ class _PatchedLoader(importlib.machinery.SourceFileLoader):
         return super().source_to_code(data, path, _optimize=_optimize)
 
 
+class _BvpLoader(importlib.machinery.SourceFileLoader):
+    """CTR_Python/CTR_Model.py:63 allocates the derivative vector with np.empty and never assigns d(u_iz)/ds, d(alpha_i)/ds of
+    a tube that is absent on a section (:80-82): the integrator then sees whatever the allocator hands back, and two runs of
+    the same configuration differ by up to 2e-5 m (measured, oracle/make_golden_bvp.py).  With DETERMINISTIC_BVP the load-time
+    substitution np.empty -> np.zeros gives those entries the value 0; everything else is the reference's file as it is."""
+
+    def get_data(self, path):
+        data = super().get_data(path)
+        if path.endswith('CTR_Model.py') and DETERMINISTIC_BVP:
+            src = data.decode()
+            old = "dydt = np.empty([20, 1])"
+            assert src.count(old) == 1, "reference CTR_Model.py:63 changed; update the loader patch"
+            data = src.replace(old, "dydt = np.zeros([20, 1])").encode()
+        return data
+
+
+DETERMINISTIC_BVP = True
+
+
 class _Finder(importlib.abc.MetaPathFinder):
     def find_spec(self, fullname, path, target=None):
+        if fullname == 'ctr_reach_envs.envs.CTR_Python.CTR_Model':
+            fn = os.path.join(REF_ROOT, 'ctr_reach_envs', 'envs', 'CTR_Python', 'CTR_Model.py')
+            return importlib.machinery.ModuleSpec(fullname, _BvpLoader(fullname, fn), origin=fn)
         if fullname != 'ctr_reach_envs.envs.model':
             return None
         fn = os.path.join(REF_ROOT, 'ctr_reach_envs', 'envs', 'model.py')
