@@ -390,59 +390,120 @@ __global__ void k_bvp_fd(const double* __restrict__ tips, int64_t n, int mode, d
                 Cm[(int64_t)(r * 3 + c) * n + i] = __ddiv_rn(__dsub_rn(tips[(int64_t)r * M + (int64_t)(base + c) * n + i], P[r]), eps_f);
 }
 
-// One Newton step of the shooting problem cost(u) = 0 on the 6-variant block (base + 5 perturbed u): solves the 5 x 5
-// forward-difference system by Gaussian elimination with partial pivoting, u += damping * du for the configurations whose
-// residual max-norm is still above f_tol (scipy.optimize.anderson's default norm and the reference's f_tol, :296).
-__global__ void k_bvp_newton(const double* __restrict__ cost, int64_t n, double eps_u, double f_tol, double damping,
-                             double* __restrict__ u, double* __restrict__ res, int32_t* __restrict__ iters,
-                             uint8_t* __restrict__ frozen, int32_t* __restrict__ active) {
+// One iteration of the shooting problem cost(u) = 0 on the 6-variant block (trial point + 5 perturbed u): Levenberg-Marquardt.
+// The trial point is accepted when its sum of squares is below that of the last accepted point; then the forward-difference
+// Jacobian of the trial point becomes the model and the damping shrinks (mu / 5).  Otherwise the damping grows (4 mu) and the
+// step is recomputed from the stored model: du = -(J^T J + mu diag(J^T J))^-1 J^T c.  Convergence is judged on the max-norm
+// (scipy.optimize.anderson's default, what the reference's f_tol refers to, CTR_Model.py:296).  Plain Newton with step
+// halving stalls on the high-twist configurations (measured on the reference's own rows: 16 of 18 against 17 of 18 here; the
+// reference's Anderson iteration itself gives up on 2 of 20).
+// st: u_base f64 [5][n] | c_base [5][n] | J [25][n] | mu [n] | merit [n]
+constexpr int BVP_LM_STATE = 37;
+__global__ void k_bvp_lm(const double* __restrict__ cost, int64_t n, double eps_u, double f_tol, int first, int last,
+                         double* __restrict__ u, double* __restrict__ st, double* __restrict__ res, int32_t* __restrict__ iters,
+                         uint8_t* __restrict__ frozen, int32_t* __restrict__ active) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n || frozen[i]) return;
     const int64_t M = 6 * n;
-    double c0[5], A[5][6];
-    double nrm = 0.0;
+    double* ub = st;
+    double* cb = st + 5 * n;
+    double* Jb = st + 10 * n;
+    double* mup = st + 35 * n;
+    double* mer = st + 36 * n;
+    double c[5], J[5][5];
+    double nrm = 0.0, ssq = 0.0;
     bool bad = false;
     for (int r = 0; r < 5; ++r) {
-        c0[r] = cost[(int64_t)r * M + i];
-        bad |= !(c0[r] == c0[r]);
-        nrm = fmax(nrm, fabs(c0[r]));
+        c[r] = cost[(int64_t)r * M + i];
+        bad |= !(c[r] == c[r]);
+        nrm = fmax(nrm, fabs(c[r]));
+        ssq += c[r] * c[r];
     }
-    res[i] = bad ? CUDART_NAN : nrm;
-    if (bad || nrm < f_tol) {
-        frozen[i] = 1;
-        return;
+    double mu;
+    if (!bad && (first || ssq < mer[i])) {                   // accept the trial point: new model
+        bool jbad = false;
+        for (int r = 0; r < 5; ++r)
+            for (int k = 0; k < 5; ++k) {
+                const double cp = cost[(int64_t)r * M + (int64_t)(1 + k) * n + i];
+                jbad |= !(cp == cp);
+                J[r][k] = (cp - c[r]) / eps_u;
+            }
+        mer[i] = ssq;
+        res[i] = nrm;
+        for (int k = 0; k < 5; ++k) {
+            ub[(int64_t)k * n + i] = u[(int64_t)k * n + i];
+            cb[(int64_t)k * n + i] = c[k];
+        }
+        if (nrm < f_tol || last || jbad) {
+            frozen[i] = 1;
+            return;
+        }
+        for (int r = 0; r < 5; ++r)
+            for (int k = 0; k < 5; ++k) Jb[(int64_t)(r * 5 + k) * n + i] = J[r][k];
+        mu = first ? 1e-2 : fmax(mup[i] * 0.2, 1e-9);
+        iters[i] += 1;
+    } else {                                                   // reject: more damping on the stored model
+        if (first) {                                           // the pass at the initial guess failed: nothing to iterate from
+            res[i] = CUDART_NAN;
+            frozen[i] = 1;
+            return;
+        }
+        mu = mup[i] * 4.0;
+        if (mu > 1e12 || last) {
+            for (int k = 0; k < 5; ++k) u[(int64_t)k * n + i] = ub[(int64_t)k * n + i];
+            frozen[i] = 1;
+            return;
+        }
+        for (int r = 0; r < 5; ++r) {
+            c[r] = cb[(int64_t)r * n + i];
+            for (int k = 0; k < 5; ++k) J[r][k] = Jb[(int64_t)(r * 5 + k) * n + i];
+        }
     }
-    for (int r = 0; r < 5; ++r) {
-        for (int c = 0; c < 5; ++c) A[r][c] = (cost[(int64_t)r * M + (int64_t)(1 + c) * n + i] - c0[r]) / eps_u;
-        A[r][5] = -c0[r];
+    mup[i] = mu;
+    double A[5][6];
+    for (int a = 0; a < 5; ++a) {
+        for (int b = 0; b < 5; ++b) {
+            double s = 0.0;
+            for (int r = 0; r < 5; ++r) s += J[r][a] * J[r][b];
+            A[a][b] = s;
+        }
+        double g = 0.0;
+        for (int r = 0; r < 5; ++r) g += J[r][a] * c[r];
+        A[a][5] = -g;
     }
+    for (int a = 0; a < 5; ++a) A[a][a] += mu * (A[a][a] + 1e-12);
+    bool singular = false;
     for (int k = 0; k < 5; ++k) {
         int piv = k;
         for (int r = k + 1; r < 5; ++r)
             if (fabs(A[r][k]) > fabs(A[piv][k])) piv = r;
-        for (int c = 0; c < 6; ++c) {
-            const double t = A[k][c];
-            A[k][c] = A[piv][c];
-            A[piv][c] = t;
+        for (int cc = 0; cc < 6; ++cc) {
+            const double t = A[k][cc];
+            A[k][cc] = A[piv][cc];
+            A[piv][cc] = t;
         }
         const double d = A[k][k];
         if (!(fabs(d) > 1e-300)) {
-            frozen[i] = 1;                                // singular Jacobian: give up on this configuration (res says how far)
-            return;
+            singular = true;
+            break;
         }
         for (int r = k + 1; r < 5; ++r) {
             const double m = A[r][k] / d;
-            for (int c = k; c < 6; ++c) A[r][c] -= m * A[k][c];
+            for (int cc = k; cc < 6; ++cc) A[r][cc] -= m * A[k][cc];
         }
+    }
+    if (singular) {
+        for (int k = 0; k < 5; ++k) u[(int64_t)k * n + i] = ub[(int64_t)k * n + i];
+        frozen[i] = 1;
+        return;
     }
     double du[5];
     for (int k = 4; k >= 0; --k) {
         double s = A[k][5];
-        for (int c = k + 1; c < 5; ++c) s -= A[k][c] * du[c];
+        for (int cc = k + 1; cc < 5; ++cc) s -= A[k][cc] * du[cc];
         du[k] = s / A[k][k];
     }
-    for (int k = 0; k < 5; ++k) u[(int64_t)k * n + i] += damping * du[k];
-    iters[i] += 1;
+    for (int k = 0; k < 5; ++k) u[(int64_t)k * n + i] = ub[(int64_t)k * n + i] + du[k];
     atomicAdd(active, 1);
 }
 

@@ -860,6 +860,17 @@ __global__ void k_reward(const double* __restrict__ ach, const double* __restric
     }
 }
 
+// float32 copy of one chunk of the result block (rows obs | achieved | desired | reward | error, f64 [rows][N]) for the opt-in
+// float32 host contract of ctr_step_host_packed_f32: half the bytes over PCIe; the float64 block on the device stays the truth
+__global__ void k_pack_f32(const double* __restrict__ blk, float* __restrict__ out, int64_t n, int64_t begin, int64_t count,
+                           int rows) {
+    const int64_t total = count * rows;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = k / count, i = begin + (k - r * count);
+        out[r * n + i] = (float)blk[r * n + i];
+    }
+}
+
 // register-resident FMA chains: the measured FP64 / FP32 FMA-pipe peak that bounds this path (no such figure in
 // MEASURED_PEAKS.json)
 template <typename T>
@@ -888,7 +899,7 @@ constexpr int N_COMPUTE_STREAMS = CTR_COMPUTE_STREAMS;   // ctr_step_host: chunk
 struct HostGraph {              // one captured ctr_step_host pipeline (keyed by the caller's host pointers)
     const void* key[8];
     int64_t per;
-    bool packed;
+    int packed;                 // 0: separate arrays, 1: one float64 block, 2: one float32 block
     bool uy0;                   // k_step instantiation captured in the kernel nodes (U_y == 0 fast path or generic)
     uint64_t stamp;
     cudaGraph_t graph;
@@ -933,6 +944,7 @@ struct ctr_handle {
     int sm_count;
     // lazily allocated staging for host calls
     float* stage_action;
+    float* stage_f32;          // device float32 copy of the result block (ctr_step_host_packed_f32)
     int64_t stage_fk_cap;
     void* stage_fk_dev;
     size_t bvp_cap;            // ctr_bvp_* scratch (bytes)
@@ -1127,6 +1139,7 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     h->use_params = 0;
     h->launches = 0;
     h->stage_action = nullptr;
+    h->stage_f32 = nullptr;
     h->stage_fk_cap = 0;
     h->stage_fk_dev = nullptr;
     h->ik_cap = 0;
@@ -1249,6 +1262,7 @@ int ctr_destroy(ctr_handle* h) {
     cudaSetDevice(h->device);
     cudaDeviceSynchronize();
     for (void* ptr : h->allocs) cudaFree(ptr);
+    if (h->stage_f32) cudaFree(h->stage_f32);
     if (h->stage_action) cudaFree(h->stage_action);      // device staging of ctr_step_host (cudaMalloc, step_host_impl)
     if (h->stage_fk_dev) cudaFree(h->stage_fk_dev);
     if (h->ik_dev) cudaFree(h->ik_dev);
@@ -1478,7 +1492,7 @@ static int copy_out(ctr_handle* h, cudaStream_t st, double* obs, double* ach, do
 // into a CUDA graph; a step is then: refresh the kernel nodes' arguments (tolerance, queue roles), one graph launch.
 static int enqueue_host_step(ctr_handle* h, const KArgs& a, int64_t per, const float* action_host, double* obs_host,
                              double* achieved_host, double* desired_host, double* reward_host, uint8_t* done_host,
-                             uint8_t* success_host, double* error_host, bool packed) {
+                             uint8_t* success_host, double* error_host, int packed) {
     const int64_t N = h->n;
     const size_t D = (size_t)h->obs_dim;
     // kernels alternate between two compute streams (the tail of one chunk overlaps the next chunk); all result copies
@@ -1498,7 +1512,16 @@ static int enqueue_host_step(ctr_handle* h, const KArgs& a, int64_t per, const f
         CTR_CUDA(cudaStreamWaitEvent(sc, h->ev_chunk[c], 0));
         cudaStream_t st = sc;
         const size_t pitch = sizeof(double) * N, w = sizeof(double) * cnt;
-        if (packed) {
+        if (packed == 2) {               // float32 block: convert the chunk's rows on its compute stream, copy half the bytes
+            k_pack_f32<<<(int)((cnt * (int64_t)(D + 8) + 1023) / 1024), 256, 0, sk>>>(h->p.obs, h->stage_f32, N, b, cnt, (int)(D + 8));
+            h->launches += 1;
+            CTR_CUDA(cudaGetLastError());
+            CTR_CUDA(cudaEventRecord(h->ev_chunk[c], sk));
+            CTR_CUDA(cudaStreamWaitEvent(sc, h->ev_chunk[c], 0));
+            float* dst = reinterpret_cast<float*>(obs_host);
+            CTR_CUDA(cudaMemcpy2DAsync(dst + b, sizeof(float) * N, h->stage_f32 + b, sizeof(float) * N, sizeof(float) * cnt, D + 8,
+                                       cudaMemcpyDeviceToHost, st));
+        } else if (packed) {
             CTR_CUDA(cudaMemcpy2DAsync(obs_host + b, pitch, h->p.obs + b, pitch, w, D + 8, cudaMemcpyDeviceToHost, st));
         } else {
             if (obs_host) CTR_CUDA(cudaMemcpy2DAsync(obs_host + b, pitch, h->p.obs + b, pitch, w, D, cudaMemcpyDeviceToHost, st));
@@ -1535,24 +1558,33 @@ static int enqueue_host_step(ctr_handle* h, const KArgs& a, int64_t per, const f
 
 static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_host, double* achieved_host,
                           double* desired_host, double* reward_host, uint8_t* done_host, uint8_t* success_host,
-                          double* error_host, bool packed);
+                          double* error_host, int packed);
 
 int ctr_step_host(ctr_handle* h, const float* action_host, double* obs_host, double* achieved_host, double* desired_host,
                   double* reward_host, uint8_t* done_host, uint8_t* success_host, double* error_host) {
     return step_host_impl(h, action_host, obs_host, achieved_host, desired_host, reward_host, done_host, success_host,
-                          error_host, false);
+                          error_host, 0);
 }
 
 int ctr_step_host_packed(ctr_handle* h, const float* action_host, double* out_f64_host, uint8_t* out_u8_host) {
     if (!h || !out_f64_host || !out_u8_host) CTR_FAIL("null argument");
     const int64_t N = h->n, D = h->obs_dim;
     return step_host_impl(h, action_host, out_f64_host, out_f64_host + D * N, out_f64_host + (D + 3) * N,
-                          out_f64_host + (D + 6) * N, out_u8_host, out_u8_host + N, out_f64_host + (D + 7) * N, true);
+                          out_f64_host + (D + 6) * N, out_u8_host, out_u8_host + N, out_f64_host + (D + 7) * N, 1);
+}
+
+int ctr_step_host_packed_f32(ctr_handle* h, const float* action_host, float* out_f32_host, uint8_t* out_u8_host) {
+    if (!h || !out_f32_host || !out_u8_host) CTR_FAIL("null argument");
+    CTR_CUDA(cudaSetDevice(h->device));
+    const int64_t N = h->n, D = h->obs_dim;
+    if (!h->stage_f32) CTR_CUDA(cudaMalloc((void**)&h->stage_f32, sizeof(float) * (size_t)(D + 8) * N));
+    double* base = reinterpret_cast<double*>(out_f32_host);      // only the block's base address is used in mode 2
+    return step_host_impl(h, action_host, base, nullptr, nullptr, nullptr, out_u8_host, out_u8_host + N, nullptr, 2);
 }
 
 static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_host, double* achieved_host,
                           double* desired_host, double* reward_host, uint8_t* done_host, uint8_t* success_host,
-                          double* error_host, bool packed) {
+                          double* error_host, int packed) {
     if (!h || !action_host) CTR_FAIL("null argument");
     CTR_CUDA(cudaSetDevice(h->device));
     const int64_t N = h->n;
@@ -1617,6 +1649,7 @@ static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_h
             if (ty != cudaGraphNodeTypeKernel) continue;
             cudaKernelNodeParams kp;
             CTR_CUDA(cudaGraphKernelNodeGetParams(nd, &kp));
+            if (kp.func == (void*)k_pack_f32) continue;          // only the k_step nodes carry per-step arguments
             const KArgs* ka = (const KArgs*)kp.kernelParams[0];
             ng.knodes.push_back(nd);
             ng.kparams.push_back(kp);
@@ -2004,7 +2037,7 @@ static BvpArgs bvp_args(ctr_handle* h, const double* q, const double* f, const d
     a.mode = mode;
     a.eps_q = 1e-4;                  // CTR_Model.py:17
     a.eps_f = 0.05;                  // CTR_Model.py:270
-    a.eps_u = 1e-6;
+    a.eps_u = 1e-4;                  // the reference's own perturbation for its (unused) shooting Jacobian, CTR_Model.py:17,243
     a.max_step = max_step;
     a.rtol = 1e-3;                   // solve_ivp defaults (no tolerances passed, CTR_Model.py:164-167)
     a.atol = 1e-6;
@@ -2064,13 +2097,14 @@ int ctr_bvp_solve(ctr_handle* h, const double* q_dev, const double* f_dev, const
     if (n <= 0) return 0;
     CTR_CUDA(cudaSetDevice(h->device));
     cudaStream_t st = (cudaStream_t)stream;
-    // scratch: tips f64 [3][6n] | cost f64 [5][6n] | active i32 [16] | frozen u8 [n]
+    // scratch: tips f64 [3][6n] | cost f64 [5][6n] | solver state f64 [37][n] | active i32 [16] | frozen u8 [n]
     char* base = nullptr;
-    int rc = bvp_scratch(h, (size_t)n * (6 * 8 * 8 + 1) + 64, &base);
+    int rc = bvp_scratch(h, (size_t)n * ((18 + 30 + BVP_LM_STATE) * 8 + 1) + 64, &base);
     if (rc) return rc;
     double* tips = (double*)base;
     double* cost = tips + 18 * n;
-    int32_t* active = (int32_t*)(cost + 30 * n);
+    double* nst = cost + 30 * n;
+    int32_t* active = (int32_t*)(nst + BVP_LM_STATE * n);
     uint8_t* frozen = (uint8_t*)(active + 16);
     BvpArgs a = bvp_args(h, q_dev, f_dev, u_dev, system_dev, params_dev, n, 4, max_step);
     a.tip = tips;
@@ -2083,8 +2117,8 @@ int ctr_bvp_solve(ctr_handle* h, const double* q_dev, const double* f_dev, const
         CTR_CUDA(cudaMemsetAsync(active, 0, sizeof(int32_t), st));
         rc = bvp_launch(h, a, st);
         if (rc) return rc;
-        k_bvp_newton<<<(int)((n + 127) / 128), 128, 0, st>>>(cost, n, a.eps_u, it == max_iters ? (double)INFINITY : f_tol, 1.0, u_dev,
-                                                              res_dev, iters_dev, frozen, active);
+        k_bvp_lm<<<(int)((n + 127) / 128), 128, 0, st>>>(cost, n, a.eps_u, f_tol, it == 0 ? 1 : 0, it == max_iters ? 1 : 0, u_dev, nst,
+                                                          res_dev, iters_dev, frozen, active);
         h->launches += 1;
         CTR_CUDA(cudaGetLastError());
         int32_t act = 0;

@@ -446,12 +446,28 @@ class CtrReachVecEnv(object):
                 'error': b[D + 7], 'done': f[0], 'is_success': f[1]}
         return self._packed_out
 
+    def alloc_host_outputs_f32(self):
+        """The same block as alloc_host_outputs() in float32 (opt-in: half the bytes over PCIe; the reference DECLARES float32
+        spaces, obs.py:89-132, but returns float64, so the float64 block stays the default contract)."""
+        N, D = self.num_envs, self.obs_dim
+        blk = torch.empty((D + 8, N), dtype=torch.float32).pin_memory()
+        flg = torch.empty((2, N), dtype=torch.uint8).pin_memory()
+        b, f = blk.numpy(), flg.numpy()
+        self._host_blocks_f32 = (blk, flg)
+        self._packed_out_f32 = {'observation': b[:D], 'achieved_goal': b[D:D + 3], 'desired_goal': b[D + 3:D + 6], 'reward': b[D + 6],
+                                'error': b[D + 7], 'done': f[0], 'is_success': f[1]}
+        return self._packed_out_f32
+
     def step_host(self, action_soa, out):
         """End-to-end step with HOST buffers (ctr_step_host): action_soa float32 [6][N] numpy (ideally pinned);
         out: dict of preallocated numpy arrays among observation [D][N], achieved_goal [3][N], desired_goal [3][N],
         reward [N], done [N] u8, is_success [N] u8, error [N].  Synchronous."""
         g = lambda k: _lib.ptr(out.get(k))
         _lib.check(self.lib.ctr_set_tolerance(self.handle, float(self.goal_tolerance.get_tol())))
+        if out is getattr(self, '_packed_out_f32', None):     # float32 block of alloc_host_outputs_f32()
+            _lib.check(self.lib.ctr_step_host_packed_f32(self.handle, _lib.ptr(action_soa), self._host_blocks_f32[0].data_ptr(),
+                                                         self._host_blocks_f32[1].data_ptr()))
+            return out
         if out is getattr(self, '_packed_out', None):         # the block layout of alloc_host_outputs()
             _lib.check(self.lib.ctr_step_host_packed(self.handle, _lib.ptr(action_soa), self._host_blocks[0].data_ptr(),
                                                      self._host_blocks[1].data_ptr()))

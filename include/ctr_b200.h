@@ -167,6 +167,10 @@ int ctr_step_host(ctr_handle *h, const float *action_host, double *obs_host, dou
  * chunk of the pipeline then needs two DMA transfers instead of seven.  (ctr_step_host pipelines too: the env range
  * is cut into chunks whose H2D / kernel / D2H overlap, and the sequence is replayed as a CUDA graph per pointer set.) */
 int ctr_step_host_packed(ctr_handle *h, const float *action_host, double *out_f64_host, uint8_t *out_u8_host);
+/* Opt-in float32 form of the packed contract: out_f32_host is float [D + 8][N] in the same row order, converted on the device
+ * from the float64 result block (which stays the handle's state and the default contract: the reference returns float64,
+ * obs.py:158-162, although it declares float32 spaces, obs.py:89-132).  Half the device->host bytes per step. */
+int ctr_step_host_packed_f32(ctr_handle *h, const float *action_host, float *out_f32_host, uint8_t *out_u8_host);
 int ctr_reset_host(ctr_handle *h, double *obs_host, double *achieved_host, double *desired_host);
 
 /* CtrReachEnv.compute_reward (ctr_reach_env.py:160-170) on arbitrary batches (HER relabelling):
@@ -245,7 +249,7 @@ int ctr_ik_dls(ctr_handle *h, const double *target_dev, double *joints_dev, cons
  * ctr_bvp_jacobian  = CTR_Model.jac (:251-262, eps 1e-4 on q, q restored by subtraction as there) and / or CTR_Model.comp
  *                     (:264-275, 0.05 N on f): J [18][n] (3 x 6 row-major) and / or C [9][n] (3 x 3), tip [3][n] optional.
  * ctr_bvp_solve     = the shooting problem of CTR_Model.minimize (:277-299): starts from the same initial guess and drives the
- *                     same 5 residuals below the same f_tol (max-norm, scipy.optimize.anderson's), by Newton steps on a
+ *                     same 5 residuals below the same f_tol (max-norm, scipy.optimize.anderson's), by Levenberg-Marquardt steps on a
  *                     forward-difference 5 x 5 Jacobian (6 passes per iteration) instead of Anderson mixing.  u [5][n] out,
  *                     res [n] final residual max-norm, iters i32 [n]; tip / cost of the pass at the solution optional.  Synchronises.
  * ctr_bvp_ik_dls    = src/jacobian_controller.py:19-53 on this model: q [6][n] in/out, target [3][n]; as ctr_ik_dls.  Synchronises. */

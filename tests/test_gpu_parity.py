@@ -648,6 +648,23 @@ def test_host_step_entry_point_matches_device_path(vec_factory, monkeypatch):
             assert np.array_equal(out['error'], info['error'].cpu().numpy())
         for k in ('joints', 'episode', 't', 'desired_joints'):
             assert torch.equal(envs[0].buffer(k), envs[1].buffer(k)), k
+    # opt-in float32 block: the float64 results rounded once to float32, flags unchanged
+    envs = [vec_factory(n, seed=6), vec_factory(n, seed=6)]
+    for e in envs:
+        e.reset()
+    out32 = envs[1].alloc_host_outputs_f32()
+    for _ in range(3):
+        act = rng.uniform(-lim, lim, size=(n, 6)).astype(np.float32)
+        obs, reward, done, info = envs[0].step(torch.tensor(act, device='cuda'))
+        torch.cuda.synchronize()
+        envs[1].step_host(np.ascontiguousarray(act.T), out32)
+        assert out32['observation'].dtype == np.float32
+        assert np.array_equal(out32['observation'].T, obs['observation'].cpu().numpy().astype(np.float32))
+        assert np.array_equal(out32['achieved_goal'].T, obs['achieved_goal'].cpu().numpy().astype(np.float32))
+        assert np.array_equal(out32['desired_goal'].T, obs['desired_goal'].cpu().numpy().astype(np.float32))
+        assert np.array_equal(out32['reward'], reward.cpu().numpy().astype(np.float32))
+        assert np.array_equal(out32['error'], info['error'].cpu().numpy().astype(np.float32))
+        assert np.array_equal(out32['done'], done.cpu().numpy()) and np.array_equal(out32['is_success'], info['is_success'].cpu().numpy().astype(np.uint8))
 
 
 def test_host_step_is_ordered_after_device_calls_on_the_callers_stream(vec_factory):
