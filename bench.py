@@ -363,12 +363,23 @@ def gpu_arm(args):
     checksum = float(out['reward'].sum())                # device->host result actually read
     h2d = 6 * 4 * N
     d2h = (D + 3 + 3 + 1 + 1) * 8 * N + 2 * N
+    # opt-in float32 result block (second entry, never the headline: the reference returns float64)
+    out32 = env.alloc_host_outputs_f32()
+    for i in range(3):
+        env.step_host(h_np[i % 4], out32)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        env.step_host(h_np[i % 4], out32)
+    torch.cuda.synchronize(dev)
+    e2e32_s = time.perf_counter() - t0
+    checksum32 = float(out32['reward'].sum())
 
     # ---- max over ranks
-    times = torch.tensor([ms, e2e_s, k_ms], dtype=torch.float64, device=dev)
+    times = torch.tensor([ms, e2e_s, k_ms, e2e32_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    ms, e2e_s, k_ms = times.tolist()
+    ms, e2e_s, k_ms, e2e32_s = times.tolist()
 
     line = None
     if rank == 0:
@@ -400,6 +411,10 @@ def gpu_arm(args):
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
                     "host_cpus_rank0": (("%d cpus local to the GPU (NVML affinity)" % len(numa_cpus)) if numa_cpus else "unbound"),
                     "api": "CtrReachVecEnv.step_host -> ctr_step_host (pinned host buffers, synchronous; chunks pipelined H2D / k_step / D2H, replayed as a CUDA graph)", "checksum": checksum},
+            "e2e_f32_results": {"value": total * e2e_steps / e2e32_s, "unit": UNIT, "h2d_bytes_per_step": h2d * world,
+                                "d2h_bytes_per_step": ((D + 8) * 4 * N + 2 * N) * world, "checksum": checksum32,
+                                "note": "opt-in contract: results converted to float32 on the device (ctr_step_host_packed_f32); NOT the headline -- "
+                                        "the reference returns float64 (obs.py:158-162)"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "fma", "kernel": "k_step<%s,%s>" % (args.precision, args.integrator), "achieved": achieved,
@@ -581,6 +596,17 @@ def kernel_table(args, dev, pool, fma_peak, hbm_peak):
     sec = timed(lambda: rep.sample(m, out=batch, call=next(calls)), reps=20, warm=3, flush=True)
     hbm_row("k_her_sample", sec, (352 + 24 + 12 + 2 * D * 8 + 3 * 24 + 24 + 8 + 1 + 16.0) * m,
             "2^20 samples from a %.0f MB ring: one record + donor goal + 3 counters in, the batch rows out" % (cap * N * 361 / 1e6))
+    # ---- BVP back-end (CTR_Python/CTR_Model.py): one shooting pass per configuration, and the 7-pass Jacobian
+    nb = 32768
+    qb = q[:, :nb].t().contiguous()
+    sec = timed(lambda: e.bvp_pass(qb), reps=5, warm=1)
+    steps_b = float(e.bvp_pass(qb)['steps'].double().sum())
+    # algorithmic flops: RK23 = 3 RHS per attempt (+2 per section start), RHS of the 20-state model ~ 330 flop (6 sincos, the
+    # two curvature sums of CTR_Model.py:84-112, R u_hat), + 20 x 12 for the stage combinations and the error norm
+    fma_row("k_bvp_pass (RK23, 20 states)", sec, steps_b * (3 * 330.0 + 240.0),
+            "%d configs, %.0f accepted steps each; one thread per pass, state in local memory" % (nb, steps_b / nb))
+    sec = timed(lambda: e.bvp_jacobian(qb[:8192], compliance=False), reps=5, warm=1)
+    fma_row("ctr_bvp_jacobian (7 passes)", sec, 7.0 * steps_b / nb * 8192 * (3 * 330.0 + 240.0), "8192 configs = 57344 passes")
     e.close()
     return tab
 

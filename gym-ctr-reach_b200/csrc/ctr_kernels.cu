@@ -320,6 +320,40 @@ __global__ void CTR_FK_BOUNDS k_fk_shape(const SysConst* __restrict__ sys, int n
     }
 }
 
+// The section table of the env path exactly as fk_group sees it (build_sections, Segment.py:6-61 + the spans of model.py:137-151):
+// t0 / tf f64 [9][n], pattern i32 [9][n] (bits 0-2 tube present, 3-5 tube curved), count i32 [n] = kept | zero-length << 8.
+__global__ void CTR_FK_BOUNDS k_segment_tables(const SysConst* __restrict__ sys, int n_systems, const double* __restrict__ joints,
+                                               const int32_t* __restrict__ system, const double* __restrict__ params, int64_t n,
+                                               double* __restrict__ t0, double* __restrict__ tf, int32_t* __restrict__ pat,
+                                               int32_t* __restrict__ count) {
+    __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
+    __shared__ GroupScratch s_gs[(BLOCK / 32) * SLOTS_PER_WARP];
+    stage_sys(s_sys, sys, n_systems);
+    const LaneId id = lane_id();
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t env = warp * ENVS_PER_WARP + id.g;
+    const bool valid = (id.g < ENVS_PER_WARP) && (env < n);
+    const int64_t e = valid ? env : 0;
+    int sysid = system ? system[e] : 0;
+    sysid = min(max(sysid, 0), n_systems - 1);
+    GroupScratch& gs = group_slot(s_gs, id);
+    double LL[6];
+    env_consts(s_sys[sysid], params, n, e, params != nullptr, id.j == 0, gs, LL);
+    double beta[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) beta[i] = joints[(int64_t)i * n + e];
+    build_sections(LL, LL + 3, beta, gs, id.j == 0);
+    if (valid) {
+        const int m = gs.nsec & 0xff;
+        for (int k = id.j; k < MAXSEC; k += 3) {
+            t0[(int64_t)k * n + env] = k < m ? gs.t0[k] : 0.0;
+            tf[(int64_t)k * n + env] = k < m ? gs.tf[k] : 0.0;
+            pat[(int64_t)k * n + env] = k < m ? gs.pat[k] : 0;
+        }
+        if (id.j == 0) count[env] = gs.nsec;
+    }
+}
+
 template <typename T, int INTEG>
 __device__ __forceinline__ void reset_envs(const KArgs& a, const LaneId& id, const SysConst* s_sys, GroupScratch* s_gs,
                                            int64_t env, bool valid, const double* __restrict__ goal,
@@ -923,6 +957,7 @@ struct ctr_handle {
     void* fields[CTR_F_COUNT];
     int64_t field_bytes[CTR_F_COUNT];
     std::vector<void*> allocs;
+    std::vector<size_t> alloc_bytes;   // same order: what a checkpoint dumps
     cudaStream_t stream;       // used by the *_host entry points (= streams[0])
     cudaStream_t streams[N_COMPUTE_STREAMS + 1];   // ctr_step_host: compute streams (chunks round-robin) + one copy-back stream
     int host_flags_late;       // ctr_step_host: done / success bytes in one copy after the last chunk ($CTR_HOST_FLAGS_LATE, default 1)
@@ -991,6 +1026,7 @@ int dev_alloc(ctr_handle* h, Tp** out, int64_t count) {
     CTR_CUDA(cudaMalloc(&ptr, bytes));
     CTR_CUDA(cudaMemset(ptr, 0, bytes));
     h->allocs.push_back(ptr);
+    h->alloc_bytes.push_back(bytes);
     *out = (Tp*)ptr;
     return 0;
 }
@@ -1757,6 +1793,104 @@ int ctr_work_counters(ctr_handle* h, double out4_host[4], void* stream) {
     out4_host[1] = tmp[ST_ATTEMPTS];
     out4_host[2] = tmp[ST_SECTIONS];
     out4_host[3] = tmp[ST_FK_COUNT];
+    return 0;
+}
+
+// ---- checkpoint / restore (joints, goals, t, system, tube parameters, RNG position, tolerance -- here: everything)
+// A checkpoint is the raw content of every device buffer the handle owns (state, result block, prefetch slots with their tags,
+// refill queues, slot permutation, statistics) plus the host-side scalars; it restores into a handle created with the same
+// configuration and env count, after which the two handles produce identical bits for identical actions.
+struct CkptHeader {
+    uint64_t magic;
+    int64_t n, step_index, n_allocs;
+    double tol;
+    uint64_t seed;
+    int32_t use_params, obs_dim, abi, pad;
+};
+static const uint64_t CKPT_MAGIC = 0x43545252424b5032ULL;   // "CTRRBKP2"
+
+int64_t ctr_checkpoint_bytes(const ctr_handle* h) {
+    if (!h) return -1;
+    size_t total = sizeof(CkptHeader) + sizeof(uint64_t) * h->alloc_bytes.size();
+    for (size_t b : h->alloc_bytes) total += b;
+    return (int64_t)total;
+}
+
+int ctr_checkpoint_save(ctr_handle* h, void* host_buf, int64_t nbytes) {
+    if (!h || !host_buf) CTR_FAIL("null argument");
+    if (nbytes < ctr_checkpoint_bytes(h)) CTR_FAIL("buffer smaller than ctr_checkpoint_bytes()");
+    CTR_CUDA(cudaSetDevice(h->device));
+    CTR_CUDA(cudaDeviceSynchronize());
+    char* p = (char*)host_buf;
+    CkptHeader hd;
+    memset(&hd, 0, sizeof hd);
+    hd.magic = CKPT_MAGIC;
+    hd.n = h->n;
+    hd.step_index = h->step_index;
+    hd.n_allocs = (int64_t)h->allocs.size();
+    hd.tol = h->tol;
+    hd.seed = h->cfg.seed;
+    hd.use_params = h->use_params;
+    hd.obs_dim = h->obs_dim;
+    hd.abi = CTR_ABI_VERSION;
+    memcpy(p, &hd, sizeof hd);
+    p += sizeof hd;
+    for (size_t b : h->alloc_bytes) {
+        const uint64_t v = b;
+        memcpy(p, &v, sizeof v);
+        p += sizeof v;
+    }
+    for (size_t k = 0; k < h->allocs.size(); ++k) {
+        CTR_CUDA(cudaMemcpy(p, h->allocs[k], h->alloc_bytes[k], cudaMemcpyDeviceToHost));
+        p += h->alloc_bytes[k];
+    }
+    return 0;
+}
+
+int ctr_checkpoint_load(ctr_handle* h, const void* host_buf, int64_t nbytes) {
+    if (!h || !host_buf) CTR_FAIL("null argument");
+    if (nbytes < (int64_t)sizeof(CkptHeader)) CTR_FAIL("truncated checkpoint");
+    const char* p = (const char*)host_buf;
+    CkptHeader hd;
+    memcpy(&hd, p, sizeof hd);
+    p += sizeof hd;
+    if (hd.magic != CKPT_MAGIC || hd.abi != CTR_ABI_VERSION) CTR_FAIL("not a checkpoint of this library version");
+    if (hd.n != h->n || hd.obs_dim != h->obs_dim || hd.n_allocs != (int64_t)h->allocs.size())
+        CTR_FAIL("checkpoint was taken from a handle with a different env count / configuration");
+    if (nbytes < ctr_checkpoint_bytes(h)) CTR_FAIL("truncated checkpoint");
+    for (size_t k = 0; k < h->allocs.size(); ++k) {
+        uint64_t v;
+        memcpy(&v, p, sizeof v);
+        p += sizeof v;
+        if (v != h->alloc_bytes[k]) CTR_FAIL("checkpoint buffer layout differs from this handle's (different configuration)");
+    }
+    CTR_CUDA(cudaSetDevice(h->device));
+    CTR_CUDA(cudaDeviceSynchronize());
+    for (size_t k = 0; k < h->allocs.size(); ++k) {
+        if (h->allocs[k] == (void*)h->sys_dev || h->allocs[k] == (void*)h->raw_dev) {   // constants of THIS handle's configuration stay
+            p += h->alloc_bytes[k];
+            continue;
+        }
+        CTR_CUDA(cudaMemcpy(h->allocs[k], p, h->alloc_bytes[k], cudaMemcpyHostToDevice));
+        p += h->alloc_bytes[k];
+    }
+    h->step_index = hd.step_index;
+    h->tol = hd.tol;
+    h->cfg.seed = hd.seed;
+    h->use_params = hd.use_params;
+    h->user_pending = 0;
+    return 0;
+}
+
+int ctr_segment_tables(ctr_handle* h, const double* joints_dev, const int32_t* system_dev, const double* params_dev, int64_t n,
+                       double* t0_dev, double* tf_dev, int32_t* pattern_dev, int32_t* count_dev, void* stream) {
+    if (!h || !joints_dev || !t0_dev || !tf_dev || !pattern_dev || !count_dev) CTR_FAIL("null argument");
+    if (n <= 0) return 0;
+    CTR_CUDA(cudaSetDevice(h->device));
+    k_segment_tables<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(h->sys_dev, h->cfg.n_systems, joints_dev, system_dev, params_dev, n,
+                                                                      t0_dev, tf_dev, pattern_dev, count_dev);
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
     return 0;
 }
 

@@ -25,7 +25,8 @@ EXPORTS = ['ctr_last_error', 'ctr_abi_version', 'ctr_create', 'ctr_destroy', 'ct
            'ctr_system_constants', 'ctr_set_tolerance', 'ctr_get_tolerance', 'ctr_seed', 'ctr_set_tube_params', 'ctr_fk',
            'ctr_fk_host', 'ctr_set_action', 'ctr_set_state_host', 'ctr_reset', 'ctr_step', 'ctr_step_strided',
            'ctr_step_host', 'ctr_step_host_packed', 'ctr_step_host_packed_f32', 'ctr_reset_host', 'ctr_compute_reward', 'ctr_relabel', 'ctr_stats', 'ctr_stats_reset',
-           'ctr_launch_count', 'ctr_work_counters', 'ctr_fault_counters', 'ctr_debug_buffer', 'ctr_measure_fma_peak', 'ctr_her_begin', 'ctr_her_store',
+           'ctr_launch_count', 'ctr_work_counters', 'ctr_fault_counters', 'ctr_debug_buffer', 'ctr_segment_tables', 'ctr_checkpoint_bytes', 'ctr_checkpoint_save',
+           'ctr_checkpoint_load', 'ctr_measure_fma_peak', 'ctr_her_begin', 'ctr_her_store',
            'ctr_her_sample', 'ctr_fk_shape', 'ctr_jacobian', 'ctr_ik_dls', 'ctr_bvp_pass', 'ctr_bvp_jacobian', 'ctr_bvp_solve',
            'ctr_bvp_ik_dls']
 
@@ -121,6 +122,11 @@ def load():
     lib.ctr_stats_reset.argtypes = [vp, vp]
     lib.ctr_work_counters.argtypes = [vp, vp, vp]
     lib.ctr_fault_counters.argtypes = [vp, vp, vp]
+    lib.ctr_segment_tables.argtypes = [vp, vp, vp, vp, i64, vp, vp, vp, vp, vp]
+    lib.ctr_checkpoint_bytes.restype = i64
+    lib.ctr_checkpoint_bytes.argtypes = [vp]
+    lib.ctr_checkpoint_save.argtypes = [vp, vp, i64]
+    lib.ctr_checkpoint_load.argtypes = [vp, vp, i64]
     lib.ctr_debug_buffer.argtypes = [vp, i32, ctypes.POINTER(vp), ctypes.POINTER(i64)]
     lib.ctr_measure_fma_peak.argtypes = [i32, i32, ctypes.POINTER(f64)]
     lib.ctr_launch_count.restype = i64
@@ -137,7 +143,7 @@ def load():
     lib.ctr_her_sample.argtypes = [vp, ctypes.POINTER(CtrHerRing), i64, i64, i32, i32, f64, ctypes.c_uint64, ctypes.c_uint64,
                                    ctypes.POINTER(CtrHerBatch), vp]
     for name in EXPORTS:
-        if name not in ('ctr_last_error', 'ctr_num_envs', 'ctr_obs_dim', 'ctr_get_tolerance', 'ctr_launch_count'):
+        if name not in ('ctr_last_error', 'ctr_num_envs', 'ctr_obs_dim', 'ctr_get_tolerance', 'ctr_launch_count', 'ctr_checkpoint_bytes'):
             getattr(lib, name).restype = ctypes.c_int
     if lib.ctr_abi_version() != ABI_VERSION:
         raise RuntimeError("libctr_b200.so ABI version mismatch")

@@ -251,6 +251,20 @@ class CtrReachVecEnv(object):
                                    _lib.ptr(tip), _lib.ptr(R), _lib.ptr(info), self._stream()))
         return (tip.t(), R.t(), info.t()) if return_info else tip.t()
 
+    def segment_tables(self, joints, system=None):
+        """Segment(...) of the reference (CTR_Python/Segment.py) as the solver uses it: joints (n, 6) -> t0 (n, 9), tf (n, 9),
+        pattern (n, 9) int32, kept (n,), zero_length (n,)."""
+        q = torch.as_tensor(joints, dtype=torch.float64, device=self.device).reshape(-1, 6).t().contiguous()
+        n = q.shape[1]
+        s = None if system is None else torch.as_tensor(system, dtype=torch.int32, device=self.device).expand(n).contiguous()
+        t0 = torch.empty((9, n), dtype=torch.float64, device=self.device)
+        tf = torch.empty((9, n), dtype=torch.float64, device=self.device)
+        pat = torch.empty((9, n), dtype=torch.int32, device=self.device)
+        cnt = torch.empty(n, dtype=torch.int32, device=self.device)
+        _lib.check(self.lib.ctr_segment_tables(self.handle, _lib.ptr(q), _lib.ptr(s), None, n, _lib.ptr(t0), _lib.ptr(tf), _lib.ptr(pat),
+                                               _lib.ptr(cnt), self._stream()))
+        return t0.t(), tf.t(), pat.t(), cnt & 0xff, cnt >> 8
+
     def backbone_shape(self, joints, system=None, max_pts=270):
         """Batched Model.r / tip_pos (model.py:66-68,137-172): joints (n, 6) -> r (n, max_pts, 3) float64 (30 samples per
         section, rows past npts[i] are unspecified), npts (n,), tip_idx (n, 3), tip (n, 3).  split_backbone() gives r1, r2, r3."""
@@ -413,6 +427,24 @@ class CtrReachVecEnv(object):
         out = (ctypes.c_double * 4)()
         _lib.check(self.lib.ctr_work_counters(self.handle, out, self._stream()))
         return dict(zip(('nfev', 'attempts', 'sections', 'fk_solves'), list(out)))
+
+    def checkpoint(self):
+        """The complete env state as one numpy uint8 array (ctr_checkpoint_save), including the goal-tolerance schedule position."""
+        nbytes = int(self.lib.ctr_checkpoint_bytes(self.handle))
+        buf = np.empty(nbytes + 16, dtype=np.uint8)
+        _lib.check(self.lib.ctr_set_tolerance(self.handle, float(self.goal_tolerance.get_tol())))
+        _lib.check(self.lib.ctr_checkpoint_save(self.handle, _lib.ptr(buf), nbytes))
+        buf[nbytes:] = np.frombuffer(np.array([self.goal_tolerance.training_step, self.goal_tolerance.current_tol], dtype=np.float64).tobytes(), dtype=np.uint8)
+        return buf
+
+    def restore(self, buf):
+        """Restore a checkpoint() taken from an env created with the same kwargs and num_envs."""
+        buf = np.ascontiguousarray(buf, dtype=np.uint8)
+        nbytes = int(self.lib.ctr_checkpoint_bytes(self.handle))
+        _lib.check(self.lib.ctr_checkpoint_load(self.handle, _lib.ptr(buf), nbytes))
+        step, tol = np.frombuffer(buf[nbytes:nbytes + 16].tobytes(), dtype=np.float64)
+        self.goal_tolerance.training_step = int(step) if float(step).is_integer() else float(step)
+        self.goal_tolerance.current_tol = float(tol)
 
     def fault_counters(self):
         """What the reference raises on, counted since the last stats_reset(): dict(fk_failed, goal_stuck, invalid_actions)."""

@@ -194,6 +194,19 @@ int ctr_work_counters(ctr_handle *h, double out4_host[4], void *stream);
  * (model.py:69 / :152-153), goal samplings stuck after 1001 draws (obs.py:204-205), env-steps whose action was NaN or
  * outside the action Box (ctr_reach_env.py:131-132), 0. */
 int ctr_fault_counters(ctr_handle *h, double out4_host[4], void *stream);
+/* Checkpoint / restore of the complete handle state: every device buffer the handle owns -- joints, goals, t,
+ * system, episode counters (= RNG position), per-env tube parameters, result block, prefetched next episodes, refill queues,
+ * slot permutation, statistics -- and the host scalars (tolerance, seed, step index).  Restores into a handle created with the
+ * same configuration and env count; the two handles then produce identical bits for identical actions.  Synchronises. */
+int64_t ctr_checkpoint_bytes(const ctr_handle *h);
+int ctr_checkpoint_save(ctr_handle *h, void *host_buf, int64_t nbytes);
+int ctr_checkpoint_load(ctr_handle *h, const void *host_buf, int64_t nbytes);
+/* Segment(t1, t2, t3, base) (CTR_Python/Segment.py:6-61) as the env path's solver sees it, for direct comparison with the
+ * reference's tables: joints f64 [6][n] (only beta is used) -> integration spans t0 / tf f64 [9][n] of the kept sections
+ * (model.py:137-151: [S_k-1, S_k - 1e-6]), pattern i32 [9][n] (bit i: tube i present, bit 3 + i: tube i curved, i.e. EI / GJ
+ * resp. U_x / U_y non-zero in the reference's tables), count i32 [n] = kept sections | zero-length spans << 8. */
+int ctr_segment_tables(ctr_handle *h, const double *joints_dev, const int32_t *system_dev, const double *params_dev, int64_t n,
+                       double *t0_dev, double *tf_dev, int32_t *pattern_dev, int32_t *count_dev, void *stream);
 /* Read-only view of the step path's internal scheduling state, for invariant tests (compute-sanitizer is not available on
  * the build pool): slot -> env permutation (i32 [N]), per-window arrival counters (i32), refill-queue counters
  * (i32 [6]: count[3], cursor[3]) and lists (i32 [capacity]), prefetch-slot episode tags (u32 [N]); CTR_DBG_STEP_INDEX

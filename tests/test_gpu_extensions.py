@@ -188,3 +188,133 @@ def test_scheduling_state_invariants_after_heavy_resets(vec_factory):
     assert (tags == ep + 1).mean() > 0.5                      # most slots are filled ahead of time
     st = env.stats(reduce=False)
     assert st['resets'] > 5 * n and env.fault_counters() == {'fk_failed': 0.0, 'goal_stuck': 0.0, 'invalid_actions': 0.0}
+
+
+def _spans_from_tables(S, EI, Ux):
+    """The reference's tables -> what the solver integrates (model.py:137-151): spans [S_k-1, S_k - 1e-6] (sorted), patterns."""
+    t0, tf, pat = [], [], []
+    prev = 0.0
+    for k in range(len(S)):
+        a, b = prev, float(S[k]) - 1e-6
+        if b < a:
+            a, b = b, a
+        prev = float(S[k])
+        if a == b:
+            continue
+        t0.append(a)
+        tf.append(b)
+        pat.append(sum(1 << i for i in range(3) if EI[i, k] != 0) | sum(8 << i for i in range(3) if Ux[i, k] != 0))
+    return t0, tf, pat
+
+
+def test_segment_tables_direct_bit_exact(golden, oracle_c, tube_constants, vec_factory):
+    """The section table the CUDA solver builds (build_sections) against the reference's Segment objects -- not through the
+    tips: the fixture's 247 tables (incl. ties, limits, sub-1e-5 sections) and 40 000 random configurations via the C oracle,
+    whose tables are themselves bit-exact against the fixture (tests/test_oracle.py)."""
+    env = vec_factory(16, select_systems=[0, 1, 2, 3])
+    g = golden('segment_reference')
+    t0, tf, pat, kept, zero = (x.cpu().numpy() for x in env.segment_tables(g['joints'].astype(np.float64), system=g['system'].astype(np.int32)))
+    for i, (q, sysid, tab) in enumerate(zip(g['joints'], g['system'], g['table'])):
+        m = int(tab[0])
+        T = tab[1:].reshape(13, 6)
+        w0, wf, wp = _spans_from_tables(T[0, :m], T[1:4, :m], T[7:10, :m])
+        assert kept[i] == len(w0) and kept[i] + zero[i] == m, i
+        assert np.array_equal(t0[i, :kept[i]], w0) and np.array_equal(tf[i, :kept[i]], wf) and pat[i, :kept[i]].tolist() == wp, i
+    rng = np.random.RandomState(31)
+    n = 40000
+    sysid = rng.randint(0, 4, size=n).astype(np.int32)
+    L = tube_constants[sysid, :3]
+    beta = np.sort(-rng.uniform(0, 1, size=(n, 3)) * (L - 1e-3), axis=1)
+    beta[::7] = np.round(beta[::7], 3)                         # breakpoints an exact multiple of 1e-5 apart
+    beta[::11, 1] = beta[::11, 0]                              # ties
+    q = np.concatenate((beta.astype(np.float32).astype(np.float64), np.zeros((n, 3))), axis=1)
+    t0, tf, pat, kept, zero = (x.cpu().numpy() for x in env.segment_tables(q, system=sysid))
+    for i in range(n):
+        S, EI, GJ, Ux, Uy = oracle_c.segment(tube_constants[sysid[i]], q[i, :3])
+        w0, wf, wp = _spans_from_tables(S, EI, Ux)
+        assert kept[i] == len(w0) and np.array_equal(t0[i, :kept[i]], w0) and np.array_equal(tf[i, :kept[i]], wf) \
+            and pat[i, :kept[i]].tolist() == wp, i
+
+
+def test_random_parts_of_reset_match_reference_distributions(golden, oracle_c, oracle_py, vec_factory):
+    """Two-sample Kolmogorov-Smirnov bounds against draws of the REFERENCE's own sample_goal / sample_parameters
+    (oracle/make_golden_stats.py).  33 marginals, Bonferroni at 1e-3 overall: D < 2.35 sqrt((n + m) / (n m))."""
+    from scipy.stats import ks_2samp
+    st = golden('stat_reference')
+    crit = lambda a, b: 2.35 * np.sqrt((len(a) + len(b)) / (len(a) * len(b)))
+    n = 32000
+    env = vec_factory(n, select_systems=[0, 1, 2, 3], seed=77)
+    env.reset()
+    torch.cuda.synchronize()
+    sysid = env.buffer('system').cpu().numpy()
+    worst = 0.0
+    for name in ('desired_joints', 'joints'):
+        q = env.buffer(name).t().cpu().numpy()
+        for s in range(4):
+            mine = q[sysid == s]
+            ref = st['goal_joints'][s]
+            assert len(mine) > 6000
+            for k in range(6):
+                D = ks_2samp(mine[:, k], ref[:, k]).statistic
+                worst = max(worst, D / crit(mine[:, k], ref[:, k]))
+                assert D < crit(mine[:, k], ref[:, k]), (name, s, k, D)
+            for a, b in ((1, 0), (2, 1)):                       # the constrained differences, not only the marginals
+                D = ks_2samp(mine[:, a] - mine[:, b], ref[:, a] - ref[:, b]).statistic
+                assert D < crit(mine[:, a], ref[:, a]), (name, s, a, b, D)
+    # domain randomisation (model_utils.py:5-35): U_x directly, EI / GJ through Tube.py:14-15 from the reference's d_i, d_o, E, G
+    env2 = vec_factory(20000, domain_rand=0.05, seed=78)
+    env2.reset()
+    torch.cuda.synchronize()
+    P = env2.buffer('tube_params').t().cpu().numpy()
+    nom = oracle_c.derive(oracle_py.DEFAULT_SYSTEMS[:1])[0]
+    R = st['param_ratio'].astype(np.float64)                    # [10000][tube][d_i, d_o, E, G, U_x]
+    sys0 = oracle_py.DEFAULT_SYSTEMS[0]
+    for i in range(3):
+        di, do = sys0[i, 2], sys0[i, 3]
+        d4 = ((R[:, i, 1] * do) ** 4 - (R[:, i, 0] * di) ** 4) / (do ** 4 - di ** 4)
+        for mine, ref, what in ((P[:, 12 + i] / nom[12 + i], R[:, i, 4], 'Ux'), (P[:, 6 + i] / nom[6 + i], R[:, i, 2] * d4, 'EI'),
+                                (P[:, 9 + i] / nom[9 + i], R[:, i, 3] * d4, 'GJ')):
+            D = ks_2samp(mine, ref).statistic
+            worst = max(worst, D / crit(mine, ref))
+            assert D < crit(mine, ref), (what, i, D)
+    assert np.array_equal(P[:, :6], np.tile(nom[:6], (20000, 1))) and np.array_equal(st['param_fixed'][:, 0], nom[:3])
+    assert worst > 0.05                                         # the statistic is being computed on something
+
+
+@pytest.mark.parametrize('extra', [dict(), dict(domain_rand=0.05, domain_rand_length=0.03, select_systems=[0, 1, 2, 3])])
+def test_checkpoint_restore_reproduces_the_run(vec_factory, extra):
+    """SURVEY.md 5 (checkpoint / resume): a restored handle continues bit for bit -- through auto-resets, i.e. the RNG position
+    (episode counters), the prefetched next episodes, the refill queues and the per-env tube parameters all travel."""
+    n = 3000
+    kw = dict(seed=21, max_steps_per_episode=6, **extra)
+    a = vec_factory(n, **kw)
+    a.goal_tolerance.current_tol = 0.04
+    a.reset()
+    g = torch.Generator(device='cuda')
+    g.manual_seed(9)
+    lim = torch.tensor(a.action_limits, device='cuda')
+    acts = [((torch.rand((n, 6), device='cuda', generator=g) * 2 - 1) * lim).contiguous() for _ in range(20)]
+    for k in range(12):
+        a.step(acts[k])
+    blob = a.checkpoint()
+    want = []
+    for k in range(12, 20):
+        obs, rew, done, info = a.step(acts[k])
+        want.append((obs['observation'].clone(), obs['desired_goal'].clone(), rew.clone(), done.clone()))
+    b = vec_factory(n, **kw)                 # fresh handle, never reset
+    b.restore(blob)
+    assert b.goal_tolerance.get_tol() == 0.04
+    for k in range(12, 20):
+        obs, rew, done, info = b.step(acts[k])
+        w = want[k - 12]
+        assert torch.equal(obs['observation'], w[0]) and torch.equal(obs['desired_goal'], w[1]), k
+        assert torch.equal(rew, w[2]) and torch.equal(done, w[3]), k
+    for name in ('joints', 'episode', 't', 'system', 'desired_joints', 'starting_joints', 'tube_params'):
+        assert torch.equal(a.buffer(name), b.buffer(name)), name
+    sa, sb = a.stats(reduce=False), b.stats(reduce=False)
+    for k in ('episodes', 'successes', 'resets', 'env_steps', 'sum_return', 'sum_length'):
+        assert sa[k] == sb[k], k                                  # (float sums and the draw counter depend on atomic order / on
+    assert abs(sa['sum_error'] - sb['sum_error']) < 1e-9 * sa['sum_error']   #  which launch happened to run a queued refill)
+    small = vec_factory(n // 2, **kw)
+    with pytest.raises(Exception):
+        small.restore(blob)
