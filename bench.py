@@ -597,7 +597,7 @@ def kernel_table(args, dev, pool, fma_peak, hbm_peak):
     hbm_row("k_her_sample", sec, (352 + 24 + 12 + 2 * D * 8 + 3 * 24 + 24 + 8 + 1 + 16.0) * m,
             "2^20 samples from a %.0f MB ring: one record + donor goal + 3 counters in, the batch rows out" % (cap * N * 361 / 1e6))
     # ---- BVP back-end (CTR_Python/CTR_Model.py): one shooting pass per configuration, and the 7-pass Jacobian
-    nb = 32768
+    nb = N
     qb = q[:, :nb].t().contiguous()
     sec = timed(lambda: e.bvp_pass(qb), reps=5, warm=1)
     steps_b = float(e.bvp_pass(qb)['steps'].double().sum())
@@ -605,8 +605,8 @@ def kernel_table(args, dev, pool, fma_peak, hbm_peak):
     # two curvature sums of CTR_Model.py:84-112, R u_hat), + 20 x 12 for the stage combinations and the error norm
     fma_row("k_bvp_pass (RK23, 20 states)", sec, steps_b * (3 * 330.0 + 240.0),
             "%d configs, %.0f accepted steps each; one thread per pass, state in local memory" % (nb, steps_b / nb))
-    sec = timed(lambda: e.bvp_jacobian(qb[:8192], compliance=False), reps=5, warm=1)
-    fma_row("ctr_bvp_jacobian (7 passes)", sec, 7.0 * steps_b / nb * 8192 * (3 * 330.0 + 240.0), "8192 configs = 57344 passes")
+    sec = timed(lambda: e.bvp_jacobian(qb[:32768], compliance=False), reps=3, warm=1)
+    fma_row("ctr_bvp_jacobian (7 passes)", sec, 7.0 * steps_b / nb * 32768 * (3 * 330.0 + 240.0), "32768 configs = 229376 passes")
     e.close()
     return tab
 

@@ -304,7 +304,13 @@ struct BvpArgs {
 
 __device__ __host__ inline int bvp_variants(int mode) { return 1 + ((mode & 1) ? 6 : 0) + ((mode & 2) ? 3 : 0) + ((mode & 4) ? 5 : 0); }
 
-__global__ void __launch_bounds__(64) k_bvp_pass(const BvpArgs a) {
+#ifndef CTR_BVP_BLOCK
+#define CTR_BVP_BLOCK 64
+#endif
+#ifndef CTR_BVP_MINB
+#define CTR_BVP_MINB 1
+#endif
+__global__ void __launch_bounds__(CTR_BVP_BLOCK, CTR_BVP_MINB) k_bvp_pass(const BvpArgs a) {
     const int V = bvp_variants(a.mode);
     const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= (int64_t)V * a.n) return;

@@ -2180,7 +2180,7 @@ static BvpArgs bvp_args(ctr_handle* h, const double* q, const double* f, const d
 }
 static int bvp_launch(ctr_handle* h, const BvpArgs& a, cudaStream_t st) {
     const int64_t total = (int64_t)bvp_variants(a.mode) * a.n;
-    k_bvp_pass<<<(int)((total + 63) / 64), 64, 0, st>>>(a);
+    k_bvp_pass<<<(int)((total + CTR_BVP_BLOCK - 1) / CTR_BVP_BLOCK), CTR_BVP_BLOCK, 0, st>>>(a);
     h->launches += 1;
     CTR_CUDA(cudaGetLastError());
     return 0;
