@@ -977,6 +977,7 @@ struct ctr_handle {
     int32_t rq_cap;
     int64_t launches;
     int sm_count;
+    int refill_blocks;         // leading blocks of a k_step launch that only drain the refill queue ($CTR_REFILL_BLOCKS, default sm_count / 2)
     // lazily allocated staging for host calls
     float* stage_action;
     float* stage_f32;          // device float32 copy of the result block (ctr_step_host_packed_f32)
@@ -1185,6 +1186,8 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     cudaDeviceProp prop;
     CTR_CUDA(cudaGetDeviceProperties(&prop, device));
     h->sm_count = prop.multiProcessorCount;
+    h->refill_blocks = getenv("CTR_REFILL_BLOCKS") ? atoi(getenv("CTR_REFILL_BLOCKS")) : h->sm_count / 2;   // sweep: profiles/r2i_refill_blocks_sweep.txt
+    if (h->refill_blocks < 0) h->refill_blocks = 0;
     h->sys_host.resize(CTR_MAX_SYSTEMS);
     memset(h->sys_host.data(), 0, sizeof(SysConst) * CTR_MAX_SYSTEMS);
     for (int s = 0; s < cfg->n_systems; ++s) derive_system(cfg->tube[s], cfg->constrain_alpha, h->sys_host[s]);
@@ -1502,7 +1505,7 @@ int ctr_step_strided(ctr_handle* h, const float* action_dev, int64_t stride_fiel
     a.act_stride_field = stride_field;
     a.act_stride_env = stride_env;
     // leading blocks drain the refill queue of the previous step first (see k_step)
-    int rc = launch_step_range(h, a, action_dev, 0, h->n, h->prefetch ? h->sm_count : 0, (cudaStream_t)stream);
+    int rc = launch_step_range(h, a, action_dev, 0, h->n, h->prefetch ? h->refill_blocks : 0, (cudaStream_t)stream);
     h->step_index += 1;
     return rc ? rc : mark_user_work(h, (cudaStream_t)stream);
 }
@@ -1542,7 +1545,7 @@ static int enqueue_host_step(ctr_handle* h, const KArgs& a, int64_t per, const f
         cudaStream_t sk = h->streams[c % N_COMPUTE_STREAMS];
         CTR_CUDA(cudaMemcpy2DAsync(h->stage_action + b, sizeof(float) * N, action_host + b, sizeof(float) * N,
                                    sizeof(float) * cnt, 6, cudaMemcpyHostToDevice, sk));
-        int rc = launch_step_range(h, a, h->stage_action, b, cnt, (c == 0 && h->prefetch) ? h->sm_count : 0, sk);
+        int rc = launch_step_range(h, a, h->stage_action, b, cnt, (c == 0 && h->prefetch) ? h->refill_blocks : 0, sk);
         if (rc) return rc;
         CTR_CUDA(cudaEventRecord(h->ev_chunk[c], sk));
         CTR_CUDA(cudaStreamWaitEvent(sc, h->ev_chunk[c], 0));
