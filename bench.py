@@ -359,10 +359,22 @@ def gpu_arm(args):
     for i in range(e2e_steps):
         env.step_host(h_np[i % 4], out)
     torch.cuda.synchronize(dev)
+    e2e_full_s = time.perf_counter() - t0
+    h2d = 6 * 4 * N
+    d2h_full = (D + 3 + 3 + 1 + 1) * 8 * N + 2 * N
+    # the headline end-to-end number: the same float64 result block through the delta contract (ctr_step_host_delta: the
+    # caller keeps the block between steps, only what a step can change crosses PCIe; content bit-identical to the full copy,
+    # tests/test_gpu_parity.py::test_host_step_entry_point_matches_device_path)
+    for i in range(3):
+        env.step_host(h_np[i % 4], out, delta=True)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        env.step_host(h_np[i % 4], out, delta=True)
+    torch.cuda.synchronize(dev)
     e2e_s = time.perf_counter() - t0
     checksum = float(out['reward'].sum())                # device->host result actually read
-    h2d = 6 * 4 * N
-    d2h = (D + 3 + 3 + 1 + 1) * 8 * N + 2 * N
+    d2h = 17 * 8 * N + 2 * N + (1 + 5 * max(N // 16, 1024)) * 8         # rows + flags + the list of changed goals
     # opt-in float32 result block (second entry, never the headline: the reference returns float64)
     out32 = env.alloc_host_outputs_f32()
     for i in range(3):
@@ -376,10 +388,10 @@ def gpu_arm(args):
     checksum32 = float(out32['reward'].sum())
 
     # ---- max over ranks
-    times = torch.tensor([ms, e2e_s, k_ms, e2e32_s], dtype=torch.float64, device=dev)
+    times = torch.tensor([ms, e2e_s, k_ms, e2e32_s, e2e_full_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    ms, e2e_s, k_ms, e2e32_s = times.tolist()
+    ms, e2e_s, k_ms, e2e32_s, e2e_full_s = times.tolist()
 
     line = None
     if rank == 0:
@@ -410,7 +422,12 @@ def gpu_arm(args):
                        "timing": "one CUDA event pair per step on the launch stream, summed; max over ranks"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
                     "host_cpus_rank0": (("%d cpus local to the GPU (NVML affinity)" % len(numa_cpus)) if numa_cpus else "unbound"),
-                    "api": "CtrReachVecEnv.step_host -> ctr_step_host (pinned host buffers, synchronous; chunks pipelined H2D / k_step / D2H, replayed as a CUDA graph)", "checksum": checksum},
+                    "api": "CtrReachVecEnv.step_host(delta=True) -> ctr_step_host_delta (pinned host buffers, synchronous; chunks pipelined H2D / k_step / D2H, "
+                           "replayed as a CUDA graph; float64 results, the caller's block is persistent and only what the step changed is copied: "
+                           "achieved | reward | error | obs rows 0..11 | flags + the goals of the envs that were reset)", "checksum": checksum},
+            "e2e_full_copy": {"value": total * e2e_steps / e2e_full_s, "unit": UNIT, "h2d_bytes_per_step": h2d * world,
+                              "d2h_bytes_per_step": d2h_full * world,
+                              "api": "CtrReachVecEnv.step_host -> ctr_step_host_packed: every result row copied every step (the round-1 headline)"},
             "e2e_f32_results": {"value": total * e2e_steps / e2e32_s, "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                                 "d2h_bytes_per_step": ((D + 8) * 4 * N + 2 * N) * world, "checksum": checksum32,
                                 "note": "opt-in contract: results converted to float32 on the device (ctr_step_host_packed_f32); NOT the headline -- "

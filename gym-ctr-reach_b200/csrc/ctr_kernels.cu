@@ -905,6 +905,24 @@ __global__ void k_pack_f32(const double* __restrict__ blk, float* __restrict__ o
     }
 }
 
+// ctr_step_host_delta: the envs of one chunk that were auto-reset in this step, i.e. whose desired goal (and system) changed:
+// list[0] = count, then (env, desired[3], system) per entry, at most cap entries (count says when the list overflowed)
+__global__ void k_delta_list(const uint8_t* __restrict__ done, const double* __restrict__ desired, const int32_t* __restrict__ system,
+                             int64_t n, int64_t begin, int64_t count, int auto_reset, int64_t cap, double* __restrict__ list) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count || !auto_reset) return;
+    const int64_t e = begin + i;
+    if (!done[e]) return;
+    const int64_t k = (int64_t)atomicAdd(list, 1.0);
+    if (k >= cap) return;
+    double* o = list + 1 + 5 * k;
+    o[0] = (double)e;
+    o[1] = desired[e];
+    o[2] = desired[n + e];
+    o[3] = desired[2 * n + e];
+    o[4] = (double)system[e];
+}
+
 // register-resident FMA chains: the measured FP64 / FP32 FMA-pipe peak that bounds this path (no such figure in
 // MEASURED_PEAKS.json)
 template <typename T>
@@ -981,6 +999,15 @@ struct ctr_handle {
     // lazily allocated staging for host calls
     float* stage_action;
     float* stage_f32;          // device float32 copy of the result block (ctr_step_host_packed_f32)
+    double* blk;               // base of the result block: achieved | reward | error | obs | desired, f64 [D + 8][N]
+    // ctr_step_host_delta: per-chunk lists of the envs whose desired goal / system changed in the step
+    double* delta_dev;         // f64 [16][DELTA_STRIDE]: count, then (env, desired[3], system) x capacity
+    double* delta_host;        // pinned mirror
+    int64_t delta_cap;         // entries per chunk
+    int64_t delta_per;         // envs per chunk of the last delta step
+    const void* delta_block;   // host block the caller's persistent copy lives in (a different pointer = full transfer)
+    double delta_tol;          // tolerance the host block's tolerance row holds
+    int delta_dirty;           // env state changed outside ctr_step_host_delta: the next call transfers everything
     int64_t stage_fk_cap;
     void* stage_fk_dev;
     size_t bvp_cap;            // ctr_bvp_* scratch (bytes)
@@ -1078,6 +1105,7 @@ KArgs make_args(const ctr_handle* h) {
 // streams.  mark_user_work() is called after a device-pointer call that writes env state; order_after_user() makes the private
 // stream wait for it, so that `ctr_reset(stream); ctr_step_host(...)` needs no synchronisation by the caller.
 int mark_user_work(ctr_handle* h, cudaStream_t st) {
+    h->delta_dirty = 1;                    // env state changed outside ctr_step_host_delta: its next call transfers everything
     if (st == h->streams[0]) return 0;
     CTR_CUDA(cudaEventRecord(h->ev_user, st));
     h->user_pending = 1;
@@ -1177,6 +1205,13 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     h->launches = 0;
     h->stage_action = nullptr;
     h->stage_f32 = nullptr;
+    h->blk = nullptr;
+    h->delta_dev = h->delta_host = nullptr;
+    h->delta_cap = 0;
+    h->delta_per = 0;
+    h->delta_block = nullptr;
+    h->delta_tol = 0.0;
+    h->delta_dirty = 1;
     h->stage_fk_cap = 0;
     h->stage_fk_dev = nullptr;
     h->ik_cap = 0;
@@ -1200,19 +1235,22 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     int rc = 0;
     rc |= dev_alloc(h, &h->sys_dev, CTR_MAX_SYSTEMS);
     rc |= dev_alloc(h, &h->raw_dev, CTR_MAX_SYSTEMS * 24);
-    // the per-step results live in ONE block, in the order obs | achieved | desired | reward | error (f64 rows) and
-    // done | success (u8 rows): a host caller whose arrays have the same order gets two DMA transfers per chunk
+    // the per-step results live in ONE block, in the order achieved | reward | error | obs | desired (f64 rows) and
+    // done | success (u8 rows): a host caller whose arrays have the same order gets two DMA transfers per chunk; what a
+    // step can leave unchanged -- the tolerance row of obs (its last or second to last row), the system row, the desired
+    // goals -- sits at the END, so that the delta contract (ctr_step_host_delta) moves one contiguous run of 17 rows
     {
         double* blk = nullptr;
         uint8_t* flg = nullptr;
         rc |= dev_alloc(h, &blk, (D + 8) * N);
         rc |= dev_alloc(h, &flg, 2 * N);
         if (!rc) {
-            h->p.obs = blk;
-            h->p.achieved = blk + D * N;
-            h->p.desired_goal = blk + (D + 3) * N;
-            h->p.reward = blk + (D + 6) * N;
-            h->p.error = blk + (D + 7) * N;
+            h->blk = blk;                                     // achieved | reward | error | obs | desired
+            h->p.achieved = blk;
+            h->p.reward = blk + 3 * N;
+            h->p.error = blk + 4 * N;
+            h->p.obs = blk + 5 * N;
+            h->p.desired_goal = blk + (5 + D) * N;
             h->p.done = flg;
             h->p.success = flg + N;
         }
@@ -1302,6 +1340,8 @@ int ctr_destroy(ctr_handle* h) {
     cudaDeviceSynchronize();
     for (void* ptr : h->allocs) cudaFree(ptr);
     if (h->stage_f32) cudaFree(h->stage_f32);
+    if (h->delta_dev) cudaFree(h->delta_dev);
+    if (h->delta_host) cudaFreeHost(h->delta_host);
     if (h->stage_action) cudaFree(h->stage_action);      // device staging of ctr_step_host (cudaMalloc, step_host_impl)
     if (h->stage_fk_dev) cudaFree(h->stage_fk_dev);
     if (h->ik_dev) cudaFree(h->ik_dev);
@@ -1454,6 +1494,7 @@ int ctr_set_state_host(ctr_handle* h, const float* joints, const double* desired
     if (desired_goal) CTR_CUDA(cudaMemcpy(h->p.desired_goal, desired_goal, sizeof(double) * 3 * h->n, cudaMemcpyHostToDevice));
     if (system) CTR_CUDA(cudaMemcpy(h->p.system, system, sizeof(int32_t) * h->n, cudaMemcpyHostToDevice));
     if (t) CTR_CUDA(cudaMemcpy(h->p.t, t, sizeof(int32_t) * h->n, cudaMemcpyHostToDevice));
+    h->delta_dirty = 1;
     return 0;
 }
 
@@ -1552,7 +1593,7 @@ static int enqueue_host_step(ctr_handle* h, const KArgs& a, int64_t per, const f
         cudaStream_t st = sc;
         const size_t pitch = sizeof(double) * N, w = sizeof(double) * cnt;
         if (packed == 2) {               // float32 block: convert the chunk's rows on its compute stream, copy half the bytes
-            k_pack_f32<<<(int)((cnt * (int64_t)(D + 8) + 1023) / 1024), 256, 0, sk>>>(h->p.obs, h->stage_f32, N, b, cnt, (int)(D + 8));
+            k_pack_f32<<<(int)((cnt * (int64_t)(D + 8) + 1023) / 1024), 256, 0, sk>>>(h->blk, h->stage_f32, N, b, cnt, (int)(D + 8));
             h->launches += 1;
             CTR_CUDA(cudaGetLastError());
             CTR_CUDA(cudaEventRecord(h->ev_chunk[c], sk));
@@ -1560,8 +1601,10 @@ static int enqueue_host_step(ctr_handle* h, const KArgs& a, int64_t per, const f
             float* dst = reinterpret_cast<float*>(obs_host);
             CTR_CUDA(cudaMemcpy2DAsync(dst + b, sizeof(float) * N, h->stage_f32 + b, sizeof(float) * N, sizeof(float) * cnt, D + 8,
                                        cudaMemcpyDeviceToHost, st));
+        } else if (packed == 3) {        // delta contract: the 17 leading rows per chunk; the list of changed goals follows the last chunk
+            CTR_CUDA(cudaMemcpy2DAsync(obs_host + b, pitch, h->blk + b, pitch, w, 17, cudaMemcpyDeviceToHost, st));
         } else if (packed) {
-            CTR_CUDA(cudaMemcpy2DAsync(obs_host + b, pitch, h->p.obs + b, pitch, w, D + 8, cudaMemcpyDeviceToHost, st));
+            CTR_CUDA(cudaMemcpy2DAsync(obs_host + b, pitch, h->blk + b, pitch, w, D + 8, cudaMemcpyDeviceToHost, st));
         } else {
             if (obs_host) CTR_CUDA(cudaMemcpy2DAsync(obs_host + b, pitch, h->p.obs + b, pitch, w, D, cudaMemcpyDeviceToHost, st));
             if (achieved_host) CTR_CUDA(cudaMemcpy2DAsync(achieved_host + b, pitch, h->p.achieved + b, pitch, w, 3, cudaMemcpyDeviceToHost, st));
@@ -1577,6 +1620,17 @@ static int enqueue_host_step(ctr_handle* h, const KArgs& a, int64_t per, const f
                 if (success_host) CTR_CUDA(cudaMemcpyAsync(success_host + b, h->p.success + b, cnt, cudaMemcpyDeviceToHost, st));
             }
         }
+    }
+    if (packed == 3) {
+        // one list for the whole env range, built on the copy stream once every chunk's kernel has finished (the stream has
+        // waited for all of them by now): per-chunk lists cost a memset, a launch and a 40 KB copy per chunk, more than the
+        // rows they save at N = 1
+        CTR_CUDA(cudaMemsetAsync(h->delta_dev, 0, sizeof(double), sc));
+        k_delta_list<<<(int)((N + 255) / 256), 256, 0, sc>>>(h->p.done, h->p.desired_goal, h->p.system, N, 0, N, h->cfg.auto_reset,
+                                                             h->delta_cap, h->delta_dev);
+        h->launches += 1;
+        CTR_CUDA(cudaGetLastError());
+        CTR_CUDA(cudaMemcpyAsync(h->delta_host, h->delta_dev, sizeof(double) * (1 + 5 * h->delta_cap), cudaMemcpyDeviceToHost, sc));
     }
     if (h->host_flags_late) {
         // the done / success bytes of ALL chunks in one copy behind the last chunk's results (the copy stream has waited for
@@ -1608,8 +1662,59 @@ int ctr_step_host(ctr_handle* h, const float* action_host, double* obs_host, dou
 int ctr_step_host_packed(ctr_handle* h, const float* action_host, double* out_f64_host, uint8_t* out_u8_host) {
     if (!h || !out_f64_host || !out_u8_host) CTR_FAIL("null argument");
     const int64_t N = h->n, D = h->obs_dim;
-    return step_host_impl(h, action_host, out_f64_host, out_f64_host + D * N, out_f64_host + (D + 3) * N,
-                          out_f64_host + (D + 6) * N, out_u8_host, out_u8_host + N, out_f64_host + (D + 7) * N, 1);
+    (void)D;
+    h->delta_dirty = 1;                                          // a full transfer into some block: the delta bookkeeping restarts
+    return step_host_impl(h, action_host, out_f64_host, nullptr, nullptr, nullptr, out_u8_host, out_u8_host + N, nullptr, 1);
+}
+
+int ctr_step_host_delta(ctr_handle* h, const float* action_host, double* out_f64_host, uint8_t* out_u8_host) {
+    if (!h || !out_f64_host || !out_u8_host) CTR_FAIL("null argument");
+    CTR_CUDA(cudaSetDevice(h->device));
+    const int64_t N = h->n, D = h->obs_dim;
+    // a different block, or env state changed by another call since the last delta step: everything is transferred once
+    if (h->user_pending) h->delta_dirty = 1;
+    if (h->delta_dirty || h->delta_block != (const void*)out_f64_host) {
+        int rc = step_host_impl(h, action_host, out_f64_host, nullptr, nullptr, nullptr, out_u8_host, out_u8_host + N, nullptr, 1);
+        if (rc) return rc;
+        h->delta_block = out_f64_host;
+        h->delta_tol = h->tol;
+        h->delta_dirty = 0;
+        return 0;
+    }
+    if (!h->delta_dev) {
+        h->delta_cap = N / 16 > 1024 ? N / 16 : 1024;            // a steady-state step resets ~1 % of the envs
+        const size_t bytes = sizeof(double) * (size_t)(1 + 5 * h->delta_cap);
+        CTR_CUDA(cudaMalloc((void**)&h->delta_dev, bytes));
+        CTR_CUDA(cudaMallocHost((void**)&h->delta_host, bytes));
+    }
+    int rc = step_host_impl(h, action_host, out_f64_host, nullptr, nullptr, nullptr, out_u8_host, out_u8_host + N, nullptr, 3);
+    if (rc) return rc;
+    // host side of the contract: the tolerance row when the tolerance changed, the goals (and system row) of the reset envs
+    double* obs = out_f64_host + 5 * N;
+    if (h->delta_tol != h->tol) {
+        double* row = obs + 12 * N;
+        for (int64_t i = 0; i < N; ++i) row[i] = h->tol;
+        h->delta_tol = h->tol;
+    }
+    double* des = out_f64_host + (5 + D) * N;
+    {
+        const double* list = h->delta_host;
+        const int64_t cnt = (int64_t)list[0];
+        if (cnt > h->delta_cap) {                                // overflow (a wave of resets): the rows are fetched whole
+            CTR_CUDA(cudaMemcpy(des, h->p.desired_goal, sizeof(double) * 3 * N, cudaMemcpyDeviceToHost));
+            if (D > 13) CTR_CUDA(cudaMemcpy(obs + 13 * N, h->p.obs + 13 * N, sizeof(double) * N, cudaMemcpyDeviceToHost));
+        } else {
+            for (int64_t k = 0; k < cnt; ++k) {
+                const double* e = list + 1 + 5 * k;
+                const int64_t env = (int64_t)e[0];
+                des[env] = e[1];
+                des[N + env] = e[2];
+                des[2 * N + env] = e[3];
+                if (D > 13) obs[13 * N + env] = e[4];
+            }
+        }
+    }
+    return 0;
 }
 
 int ctr_step_host_packed_f32(ctr_handle* h, const float* action_host, float* out_f32_host, uint8_t* out_u8_host) {
@@ -1627,12 +1732,14 @@ static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_h
     if (!h || !action_host) CTR_FAIL("null argument");
     CTR_CUDA(cudaSetDevice(h->device));
     const int64_t N = h->n;
+    if (packed != 3) h->delta_dirty = 1;   // (ctr_step_host_delta clears it again after its own full transfer)
     if (!h->stage_action) CTR_CUDA(cudaMalloc((void**)&h->stage_action, sizeof(float) * 6 * N));
     int64_t chunks = h->host_chunks > 0 ? h->host_chunks : N / 16384;
     if (chunks < 1) chunks = 1;
     if (chunks > 16) chunks = 16;
     int64_t per = (N + chunks - 1) / chunks;
     per = ((per + SORT_WINDOW - 1) / SORT_WINDOW) * SORT_WINDOW;      // chunks start on sorting-window boundaries
+    if (packed == 3) h->delta_per = per;
     const KArgs a = make_args(h);
     cudaStream_t s0 = h->streams[0];
     {   // env state written by device-pointer calls on the caller's stream (reset, step, tube parameters) comes first
@@ -1688,7 +1795,7 @@ static int step_host_impl(ctr_handle* h, const float* action_host, double* obs_h
             if (ty != cudaGraphNodeTypeKernel) continue;
             cudaKernelNodeParams kp;
             CTR_CUDA(cudaGraphKernelNodeGetParams(nd, &kp));
-            if (kp.func == (void*)k_pack_f32) continue;          // only the k_step nodes carry per-step arguments
+            if (kp.func == (void*)k_pack_f32 || kp.func == (void*)k_delta_list) continue;   // only the k_step nodes carry per-step arguments
             const KArgs* ka = (const KArgs*)kp.kernelParams[0];
             ng.knodes.push_back(nd);
             ng.kparams.push_back(kp);
@@ -1882,6 +1989,7 @@ int ctr_checkpoint_load(ctr_handle* h, const void* host_buf, int64_t nbytes) {
     h->cfg.seed = hd.seed;
     h->use_params = hd.use_params;
     h->user_pending = 0;
+    h->delta_dirty = 1;
     return 0;
 }
 

@@ -24,7 +24,7 @@ REWARD = {'sparse': 0, 'dense': 1}
 EXPORTS = ['ctr_last_error', 'ctr_abi_version', 'ctr_create', 'ctr_destroy', 'ctr_num_envs', 'ctr_obs_dim', 'ctr_buffer',
            'ctr_system_constants', 'ctr_set_tolerance', 'ctr_get_tolerance', 'ctr_seed', 'ctr_set_tube_params', 'ctr_fk',
            'ctr_fk_host', 'ctr_set_action', 'ctr_set_state_host', 'ctr_reset', 'ctr_step', 'ctr_step_strided',
-           'ctr_step_host', 'ctr_step_host_packed', 'ctr_step_host_packed_f32', 'ctr_reset_host', 'ctr_compute_reward', 'ctr_relabel', 'ctr_stats', 'ctr_stats_reset',
+           'ctr_step_host', 'ctr_step_host_packed', 'ctr_step_host_packed_f32', 'ctr_step_host_delta', 'ctr_reset_host', 'ctr_compute_reward', 'ctr_relabel', 'ctr_stats', 'ctr_stats_reset',
            'ctr_launch_count', 'ctr_work_counters', 'ctr_fault_counters', 'ctr_debug_buffer', 'ctr_segment_tables', 'ctr_checkpoint_bytes', 'ctr_checkpoint_save',
            'ctr_checkpoint_load', 'ctr_measure_fma_peak', 'ctr_her_begin', 'ctr_her_store',
            'ctr_her_sample', 'ctr_fk_shape', 'ctr_jacobian', 'ctr_ik_dls', 'ctr_bvp_pass', 'ctr_bvp_jacobian', 'ctr_bvp_solve',
@@ -115,6 +115,7 @@ def load():
     lib.ctr_step_host.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.ctr_step_host_packed.argtypes = [vp, vp, vp, vp]
     lib.ctr_step_host_packed_f32.argtypes = [vp, vp, vp, vp]
+    lib.ctr_step_host_delta.argtypes = [vp, vp, vp, vp]
     lib.ctr_reset_host.argtypes = [vp, vp, vp, vp]
     lib.ctr_compute_reward.argtypes = [vp, vp, vp, i64, f64, i32, vp, vp]
     lib.ctr_relabel.argtypes = [vp, vp, vp, i64, f64, i32, vp, vp, vp]

@@ -466,16 +466,16 @@ class CtrReachVecEnv(object):
         return (t.to(torch.int64) & 0xFFFFFFFF) if which == 6 else t
 
     def alloc_host_outputs(self):
-        """Pinned host arrays for step_host(), laid out like the device's result block (observation | achieved_goal |
-        desired_goal | reward | error as float64 rows, done | is_success as uint8 rows) so that ctr_step_host moves
+        """Pinned host arrays for step_host(), laid out like the device's result block (achieved_goal | reward | error |
+        observation | desired_goal as float64 rows, done | is_success as uint8 rows) so that ctr_step_host moves
         each chunk's results with two DMA transfers instead of seven."""
         N, D = self.num_envs, self.obs_dim
         blk = torch.empty((D + 8, N), dtype=torch.float64).pin_memory()
         flg = torch.empty((2, N), dtype=torch.uint8).pin_memory()
         b, f = blk.numpy(), flg.numpy()
         self._host_blocks = (blk, flg)           # keep the pinned storage alive
-        self._packed_out = {'observation': b[:D], 'achieved_goal': b[D:D + 3], 'desired_goal': b[D + 3:D + 6], 'reward': b[D + 6],
-                'error': b[D + 7], 'done': f[0], 'is_success': f[1]}
+        self._packed_out = {'achieved_goal': b[0:3], 'reward': b[3], 'error': b[4], 'observation': b[5:5 + D],
+                            'desired_goal': b[5 + D:8 + D], 'done': f[0], 'is_success': f[1]}
         return self._packed_out
 
     def alloc_host_outputs_f32(self):
@@ -486,19 +486,28 @@ class CtrReachVecEnv(object):
         flg = torch.empty((2, N), dtype=torch.uint8).pin_memory()
         b, f = blk.numpy(), flg.numpy()
         self._host_blocks_f32 = (blk, flg)
-        self._packed_out_f32 = {'observation': b[:D], 'achieved_goal': b[D:D + 3], 'desired_goal': b[D + 3:D + 6], 'reward': b[D + 6],
-                                'error': b[D + 7], 'done': f[0], 'is_success': f[1]}
+        self._packed_out_f32 = {'achieved_goal': b[0:3], 'reward': b[3], 'error': b[4], 'observation': b[5:5 + D],
+                                'desired_goal': b[5 + D:8 + D], 'done': f[0], 'is_success': f[1]}
         return self._packed_out_f32
 
-    def step_host(self, action_soa, out):
+    def step_host(self, action_soa, out, delta=False):
         """End-to-end step with HOST buffers (ctr_step_host): action_soa float32 [6][N] numpy (ideally pinned);
         out: dict of preallocated numpy arrays among observation [D][N], achieved_goal [3][N], desired_goal [3][N],
-        reward [N], done [N] u8, is_success [N] u8, error [N].  Synchronous."""
+        reward [N], done [N] u8, is_success [N] u8, error [N].  Synchronous.
+        delta=True (only with the block of alloc_host_outputs(), which the caller must leave untouched between steps): the
+        same float64 content with fewer bytes moved -- goals are patched for the envs that were reset, the tolerance row is
+        rewritten on the host when it changed (ctr_step_host_delta)."""
         g = lambda k: _lib.ptr(out.get(k))
         _lib.check(self.lib.ctr_set_tolerance(self.handle, float(self.goal_tolerance.get_tol())))
         if out is getattr(self, '_packed_out_f32', None):     # float32 block of alloc_host_outputs_f32()
             _lib.check(self.lib.ctr_step_host_packed_f32(self.handle, _lib.ptr(action_soa), self._host_blocks_f32[0].data_ptr(),
                                                          self._host_blocks_f32[1].data_ptr()))
+            return out
+        if delta:
+            if out is not getattr(self, '_packed_out', None):
+                raise ValueError("delta=True needs the block returned by alloc_host_outputs()")
+            _lib.check(self.lib.ctr_step_host_delta(self.handle, _lib.ptr(action_soa), self._host_blocks[0].data_ptr(),
+                                                    self._host_blocks[1].data_ptr()))
             return out
         if out is getattr(self, '_packed_out', None):         # the block layout of alloc_host_outputs()
             _lib.check(self.lib.ctr_step_host_packed(self.handle, _lib.ptr(action_soa), self._host_blocks[0].data_ptr(),

@@ -163,10 +163,18 @@ int ctr_step_strided(ctr_handle *h, const float *action_dev, int64_t stride_fiel
 int ctr_step_host(ctr_handle *h, const float *action_host, double *obs_host, double *achieved_host, double *desired_host,
                   double *reward_host, uint8_t *done_host, uint8_t *success_host, double *error_host);
 /* Same step, results into TWO host blocks laid out like the device's result block: out_f64 = f64 [(D + 8)][N] with rows
- * obs (D) | achieved (3) | desired (3) | reward (1) | error (1); out_u8 = u8 [2][N] with rows done | success.  Each
+ * achieved (3) | reward (1) | error (1) | obs (D) | desired (3); out_u8 = u8 [2][N] with rows done | success.  Each
  * chunk of the pipeline then needs two DMA transfers instead of seven.  (ctr_step_host pipelines too: the env range
  * is cut into chunks whose H2D / kernel / D2H overlap, and the sequence is replayed as a CUDA graph per pointer set.) */
 int ctr_step_host_packed(ctr_handle *h, const float *action_host, double *out_f64_host, uint8_t *out_u8_host);
+/* Opt-in DELTA form of the packed contract (float64, same block layout): the caller passes the SAME two blocks every step and
+ * keeps their content; the library transfers only what a step can change -- achieved | reward | error | obs rows 0..11 and the
+ * flags -- patches desired_goal (and the system row of obs) for the envs that were auto-reset in this step from a short
+ * device-built list, and rewrites the tolerance row of obs on the host when the tolerance changed.  After the call the blocks
+ * hold exactly what ctr_step_host_packed would have written (tests compare them bit for bit); 138 instead of 170 bytes per
+ * env-step cross PCIe.  The first call, a call with different blocks, and the first call after any other call that changes
+ * env state (ctr_reset*, ctr_step*, ctr_set_state_host, ctr_set_tube_params, ctr_checkpoint_load) transfer everything. */
+int ctr_step_host_delta(ctr_handle *h, const float *action_host, double *out_f64_host, uint8_t *out_u8_host);
 /* Opt-in float32 form of the packed contract: out_f32_host is float [D + 8][N] in the same row order, converted on the device
  * from the float64 result block (which stays the handle's state and the default contract: the reference returns float64,
  * obs.py:158-162, although it declares float32 spaces, obs.py:89-132).  Half the device->host bytes per step. */

@@ -648,6 +648,28 @@ def test_host_step_entry_point_matches_device_path(vec_factory, monkeypatch):
             assert np.array_equal(out['error'], info['error'].cpu().numpy())
         for k in ('joints', 'episode', 't', 'desired_joints'):
             assert torch.equal(envs[0].buffer(k), envs[1].buffer(k)), k
+    # delta contract: the same float64 block content with fewer bytes moved -- through auto-resets (4-step episodes), a tolerance
+    # change, a second system row, an interleaved explicit reset and a device-side step (both force one full transfer)
+    for kw in (dict(), dict(select_systems=[0, 1, 2, 3], max_steps_per_episode=4)):
+        envs = [vec_factory(n, seed=8, **kw), vec_factory(n, seed=8, **kw)]
+        for e in envs:
+            e.goal_tolerance.current_tol = 0.03
+            e.reset()
+        full, dl = envs[0].alloc_host_outputs(), envs[1].alloc_host_outputs()
+        for it in range(9):
+            act = np.ascontiguousarray(rng.uniform(-lim, lim, size=(n, 6)).astype(np.float32).T)
+            if it == 4:
+                for e in envs:
+                    e.goal_tolerance.current_tol = 0.01
+            if it == 6:
+                for e in envs:
+                    e.reset(mask=(torch.arange(n, device='cuda') % 3 == 0).to(torch.uint8))
+                    e.step(torch.tensor(act.T.copy(), device='cuda'))
+            envs[0].step_host(act, full)
+            envs[1].step_host(act, dl, delta=True)
+            for k in full:
+                assert np.array_equal(full[k], dl[k]), (kw, it, k)
+        assert float(full['done'].sum()) > 0
     # opt-in float32 block: the float64 results rounded once to float32, flags unchanged
     envs = [vec_factory(n, seed=6), vec_factory(n, seed=6)]
     for e in envs:
