@@ -91,15 +91,21 @@ __global__ void __launch_bounds__(32 * HER_WARPS) k_her_store(const ctr_her_ring
         float* act = reinterpret_cast<float*>(me + 2 * D + 10);
 #pragma unroll
         for (int i = 0; i < 6; ++i) act[i] = action[(int64_t)i * stride_field + e * stride_env];
-        for (int d = 2 * D + 13; d < HER_REC; ++d) me[d] = 0.0;   // padding: defined bytes
+        for (int d = 2 * D + 13; d < HER_REC - 2; ++d) me[d] = 0.0;   // padding: defined bytes
         r.done[col] = done ? 1 : 0;
         const int t = r.cur_t[e] + 1;
         r.t_in_ep[col] = t;
+        // the sampler's index arithmetic needs (t_in_ep, ep_len, done) of a transition BEFORE it can fetch anything else: a copy
+        // in the record's last 16 bytes makes that ONE sector of the record it reads anyway instead of three 4- / 1-byte
+        // gathers from the side arrays (which stay authoritative for host-side readers)
+        me[HER_REC - 2] = done ? 1.0 : 0.0;
+        me[HER_REC - 1] = __hiloint2double(done ? t : 0, t);       // high word: ep_len (0 = episode still open), low word: t_in_ep
         if (done) {                               // close the episode: every transition of it learns its length
             const int back = t < (int)r.capacity ? t : (int)r.capacity;
             int64_t sl = slot;
             for (int k = 0; k < back; ++k) {
                 r.ep_len[sl * n + e] = t;
+                if (k > 0) reinterpret_cast<int32_t*>(r.rec + (sl * n + e) * HER_REC + (HER_REC - 1))[1] = t;   // the record's copy
                 sl = (sl == 0) ? r.capacity - 1 : sl - 1;
             }
             r.cur_t[e] = 0;
@@ -118,7 +124,8 @@ __global__ void __launch_bounds__(32 * HER_WARPS) k_her_store(const ctr_her_ring
 // key = seed -> x: slot age, y: env, z: relabel coin, w: future offset; integer ranges by multiply-shift) and reads the three
 // integers the index arithmetic needs.  Phase 2: the warp copies the 32 records into shared memory, one record per iteration,
 // 352 coalesced bytes each (+ the donor's next_achieved for relabelled samples).  Phase 3: every output row is written by the
-// 32 lanes at once (256 contiguous bytes).  A sample costs ~15 sectors of reads instead of one sector per 8-byte element.
+// 32 lanes at once (256 contiguous bytes).  A sample costs 13 sectors of reads (11 of its record, whose last one is also what
+// phase 1 needs, the env's open-episode counter, the donor's goal) instead of one sector per 8-byte element.
 __global__ void __launch_bounds__(32 * HER_WARPS) k_her_sample(const ctr_her_ring r, const ctr_her_batch b, int64_t n_stored,
                                                               int64_t newest_slot, int n_goal, int rewrite_error, double tol,
                                                               int reward_mode, uint2 key, uint2 call) {
@@ -132,7 +139,7 @@ __global__ void __launch_bounds__(32 * HER_WARPS) k_her_sample(const ctr_her_rin
     const int D = r.obs_dim;
     // ---- phase 1
     int64_t col = 0, gcol = -1;
-    bool relabel = false;
+    bool relabel = false, done_rec = false;
     if (live) {
         const uint4 u = philox4x32(make_uint4((unsigned)i, (unsigned)((uint64_t)i >> 32), call.x, call.y), key);
         const int64_t age = (int64_t)(((uint64_t)u.x * (uint64_t)n_stored) >> 32);
@@ -140,8 +147,10 @@ __global__ void __launch_bounds__(32 * HER_WARPS) k_her_sample(const ctr_her_rin
         if (slot < 0) slot += r.capacity;
         const int64_t env = (int64_t)(((uint64_t)u.y * (uint64_t)n) >> 32);
         col = slot * n + env;
-        const int k = r.t_in_ep[col];
-        int L = r.ep_len[col];
+        const double2 tail = __ldg(reinterpret_cast<const double2*>(r.rec + col * HER_REC + (HER_REC - 2)));
+        done_rec = tail.x != 0.0;
+        const int k = __double2loint(tail.y);
+        int L = __double2hiint(tail.y);
         if (L == 0) L = r.cur_t[env];                             // open episode: the transitions stored so far
         relabel = (k < L) && ((((uint64_t)u.z * (uint64_t)(n_goal + 1)) >> 32) < (uint64_t)n_goal);
         if (relabel) {
@@ -183,7 +192,7 @@ __global__ void __launch_bounds__(32 * HER_WARPS) k_her_sample(const ctr_her_rin
         goal[c] = relabel ? s_goal[w][lane][c] : me[2 * D + 6 + c];
     }
     double reward = me[2 * D + 9];
-    uint8_t done = live ? r.done[col] : 0;
+    uint8_t done = (live && done_rec) ? 1 : 0;
     if (relabel) {                                                // ctr_reach_env.py:168-170 on (next achieved, new goal)
         const double x = __dsub_rn(nach[0], goal[0]), y = __dsub_rn(nach[1], goal[1]), z = __dsub_rn(nach[2], goal[2]);
         const double dist = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)), __dmul_rn(z, z)));

@@ -90,6 +90,7 @@ class CtrReachEnv(object):
         self.length_based_sample = length_based_sample
         self.domain_rand = domain_rand
         self.model = _ModelView(self)
+        self._host_out = None
         self.visualization = None
         self.t = 0
         self.trig_obj = _TrigObjView(self)
@@ -141,12 +142,15 @@ class CtrReachEnv(object):
     def step(self, action):
         assert not np.all(np.isnan(action))
         assert self.action_space.contains(action)
-        a = np.asarray(action, dtype=np.float32).reshape(1, 6)
-        self._vec.step(a)
+        a = np.asarray(action, dtype=np.float32).reshape(6, 1)
+        if self._host_out is None:
+            self._host_out = self._vec.alloc_host_outputs()
+        b = self._vec.step_host(a, self._host_out)               # one synchronous call: results arrive in pinned host arrays
         self.t += 1
         self.model._note(self.trig_obj.joints, self.system)      # ctr_reach_env.py:137
-        b = self._pull(('reward', 'done', 'is_success', 'error'))
-        obs = self._obs()
+        obs = {'observation': b['observation'][:, 0].copy(), 'achieved_goal': b['achieved_goal'][:, 0].copy(),
+               'desired_goal': b['desired_goal'][:, 0].copy()}
+        self.trig_obj.obs = obs
         reward = np.float64(b['reward'][0])
         done = bool(b['done'][0])
         if self.evaluation:

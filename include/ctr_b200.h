@@ -294,8 +294,11 @@ int ctr_bvp_ik_dls(ctr_handle *h, const double *target_dev, double *q_dev, const
  * transition (slot, env) is record number slot * n_envs + env; a record is CTR_HER_RECORD doubles (352 bytes = 11 aligned
  * 32-byte sectors), so that sampling -- a gather of random records -- moves whole sectors:
  *   [0, D) obs | [D, 2D) next_obs | 2D + 0..2 achieved | 2D + 3..5 next_achieved | 2D + 6..8 desired | 2D + 9 reward |
- *   2D + 10..12 action (6 x f32 packed in 3 doubles) | padding.
- * The few integers the index arithmetic needs before it touches a record stay in separate arrays. */
+ *   2D + 10..12 action (6 x f32 packed in 3 doubles) | padding | 42 done (0.0 / 1.0) | 43 (t_in_ep as the low, ep_len as the
+ *   high 32-bit word).
+ * The integers the index arithmetic needs before it can fetch anything else (done, t_in_ep, ep_len) live in the separate
+ * arrays below -- the authoritative copy, for host-side readers -- AND in the last 16 bytes of the record, which is what the
+ * sampler reads: one sector of the record it fetches anyway instead of three scattered 1- / 4-byte gathers. */
 #define CTR_HER_RECORD 44
 typedef struct {
     int64_t n_envs, capacity;      /* capacity = number of step slots                                            */
