@@ -374,7 +374,7 @@ def gpu_arm(args):
     torch.cuda.synchronize(dev)
     e2e_s = time.perf_counter() - t0
     checksum = float(out['reward'].sum())                # device->host result actually read
-    d2h = 17 * 8 * N + 2 * N + (1 + 5 * max(N // 16, 1024)) * 8         # rows + flags + the list of changed goals
+    d2h = 17 * 8 * N + 2 * N + (1 + 5 * max(N // 64, 1024)) * 8         # rows + flags + the list of changed goals
     # opt-in float32 result block (second entry, never the headline: the reference returns float64)
     out32 = env.alloc_host_outputs_f32()
     for i in range(3):
