@@ -354,12 +354,19 @@ def gpu_arm(args):
     for i in range(3):
         env.step_host(h_np[i % 4], out)
     barrier()
-    e2e_steps = args.steps
-    t0 = time.perf_counter()
-    for i in range(e2e_steps):
-        env.step_host(h_np[i % 4], out)
-    torch.cuda.synchronize(dev)
-    e2e_full_s = time.perf_counter() - t0
+    e2e_steps = max(args.steps, 100)      # wall-clock loops: at least 100 calls (60 ms), a host hiccup of 0.3 ms is 40 % of one call
+
+    def e2e_loop(**kw):
+        per = []
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            t1 = time.perf_counter()
+            env.step_host(h_np[i % 4], kw['o'], delta=kw['d'])
+            per.append(time.perf_counter() - t1)
+        torch.cuda.synchronize(dev)
+        return time.perf_counter() - t0, sorted(per)[len(per) // 2]
+
+    e2e_full_s, med_full = e2e_loop(o=out, d=False)
     h2d = 6 * 4 * N
     d2h_full = (D + 3 + 3 + 1 + 1) * 8 * N + 2 * N
     # the headline end-to-end number: the same float64 result block through the delta contract (ctr_step_host_delta: the
@@ -368,11 +375,7 @@ def gpu_arm(args):
     for i in range(3):
         env.step_host(h_np[i % 4], out, delta=True)
     barrier()
-    t0 = time.perf_counter()
-    for i in range(e2e_steps):
-        env.step_host(h_np[i % 4], out, delta=True)
-    torch.cuda.synchronize(dev)
-    e2e_s = time.perf_counter() - t0
+    e2e_s, med_delta = e2e_loop(o=out, d=True)
     checksum = float(out['reward'].sum())                # device->host result actually read
     d2h = 17 * 8 * N + 2 * N + (1 + 5 * max(N // 64, 1024)) * 8         # rows + flags + the list of changed goals
     # opt-in float32 result block (second entry, never the headline: the reference returns float64)
@@ -380,11 +383,7 @@ def gpu_arm(args):
     for i in range(3):
         env.step_host(h_np[i % 4], out32)
     barrier()
-    t0 = time.perf_counter()
-    for i in range(e2e_steps):
-        env.step_host(h_np[i % 4], out32)
-    torch.cuda.synchronize(dev)
-    e2e32_s = time.perf_counter() - t0
+    e2e32_s, med_f32 = e2e_loop(o=out32, d=False)
     checksum32 = float(out32['reward'].sum())
 
     # ---- max over ranks
@@ -421,14 +420,15 @@ def gpu_arm(args):
                        "episode_phase": "t = global env index mod 150 before warm-up (steady-state reset load, no synchronised refill wave)",
                        "timing": "one CUDA event pair per step on the launch stream, summed; max over ranks"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
+                    "calls": e2e_steps, "median_ms_per_call_rank0": med_delta * 1e3,
                     "host_cpus_rank0": (("%d cpus local to the GPU (NVML affinity)" % len(numa_cpus)) if numa_cpus else "unbound"),
                     "api": "CtrReachVecEnv.step_host(delta=True) -> ctr_step_host_delta (pinned host buffers, synchronous; chunks pipelined H2D / k_step / D2H, "
                            "replayed as a CUDA graph; float64 results, the caller's block is persistent and only what the step changed is copied: "
                            "achieved | reward | error | obs rows 0..11 | flags + the goals of the envs that were reset)", "checksum": checksum},
-            "e2e_full_copy": {"value": total * e2e_steps / e2e_full_s, "unit": UNIT, "h2d_bytes_per_step": h2d * world,
+            "e2e_full_copy": {"value": total * e2e_steps / e2e_full_s, "unit": UNIT, "median_ms_per_call_rank0": med_full * 1e3, "h2d_bytes_per_step": h2d * world,
                               "d2h_bytes_per_step": d2h_full * world,
                               "api": "CtrReachVecEnv.step_host -> ctr_step_host_packed: every result row copied every step (the round-1 headline)"},
-            "e2e_f32_results": {"value": total * e2e_steps / e2e32_s, "unit": UNIT, "h2d_bytes_per_step": h2d * world,
+            "e2e_f32_results": {"value": total * e2e_steps / e2e32_s, "unit": UNIT, "median_ms_per_call_rank0": med_f32 * 1e3, "h2d_bytes_per_step": h2d * world,
                                 "d2h_bytes_per_step": ((D + 8) * 4 * N + 2 * N) * world, "checksum": checksum32,
                                 "note": "opt-in contract: results converted to float32 on the device (ctr_step_host_packed_f32); NOT the headline -- "
                                         "the reference returns float64 (obs.py:158-162)"},
