@@ -321,6 +321,9 @@ __device__ __forceinline__ void cswap(double& a, double& b) {
 
 // L, Lc: tube lengths / curved lengths; beta: float64 joint extensions.  All lanes of the group compute the same
 // values; `writer` (one lane) stores them.  Ends with __syncwarp() so the group can read the table.
+// GAP = false: the spans of the BVP model, [S_k-1, S_k] without the 1e-6 gap of model.py:141 (CTR_Model.py:164-167).
+// SYNC = false: called by some groups of the warp only; the caller synchronises before the table is read.
+template <bool GAP = true, bool SYNC = true>
 __device__ __forceinline__ void build_sections(const double* L, const double* Lc, const double* beta, GroupScratch& gs,
                                                bool writer) {
     double p[10], dtip[3], dc[3];
@@ -363,8 +366,8 @@ __device__ __forceinline__ void build_sections(const double* L, const double* Lc
                 pat |= (curved ? 8 : 0) << i;
             }
             double t0 = prevS;
-            double tf = __dsub_rn(S, 1e-6);                                              // model.py:141
-            if (tf < t0) {                                                               // model.py:145-151: sorted span
+            double tf = GAP ? __dsub_rn(S, 1e-6) : S;                                    // model.py:141
+            if (GAP && tf < t0) {                                                        // model.py:145-151: sorted span
                 const double z = t0;
                 t0 = tf;
                 tf = z;
@@ -383,7 +386,7 @@ __device__ __forceinline__ void build_sections(const double* L, const double* Lc
         }
     }
     if (writer) gs.nsec = m | (skipped << 8);
-    __syncwarp();
+    if (SYNC) __syncwarp();
 }
 
 // ---- per-section constants in the lane-rotated form -----------------------------------------------------------

@@ -1012,6 +1012,7 @@ struct ctr_handle {
     void* stage_fk_dev;
     size_t bvp_cap;            // ctr_bvp_* scratch (bytes)
     void* bvp_dev;
+    unsigned long long* bvp_next;   // work counter of k_bvp_pass_g
     int64_t ik_cap;            // ctr_jacobian / ctr_ik_dls scratch: joints f64 [6][7n] | tips f64 [3][7n] | system i32 [7n] | frozen u8 [n] | active i32
     void* ik_dev;
 };
@@ -1218,6 +1219,7 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     h->ik_dev = nullptr;
     h->bvp_cap = 0;
     h->bvp_dev = nullptr;
+    h->bvp_next = nullptr;
     cudaDeviceProp prop;
     CTR_CUDA(cudaGetDeviceProperties(&prop, device));
     h->sm_count = prop.multiProcessorCount;
@@ -1346,6 +1348,7 @@ int ctr_destroy(ctr_handle* h) {
     if (h->stage_fk_dev) cudaFree(h->stage_fk_dev);
     if (h->ik_dev) cudaFree(h->ik_dev);
     if (h->bvp_dev) cudaFree(h->bvp_dev);
+    if (h->bvp_next) cudaFree(h->bvp_next);
     if (h->stream) cudaStreamDestroy(h->stream);
     for (int k = 1; k <= N_COMPUTE_STREAMS; ++k) {
         if (h->streams[k]) cudaStreamDestroy(h->streams[k]);
@@ -2289,9 +2292,23 @@ static BvpArgs bvp_args(ctr_handle* h, const double* q, const double* f, const d
     a.fault = h->p.stats + ST_FK_FAILED;
     return a;
 }
-static int bvp_launch(ctr_handle* h, const BvpArgs& a, cudaStream_t st) {
+static int bvp_launch(ctr_handle* h, const BvpArgs& a_in, cudaStream_t st) {
+    BvpArgs a = a_in;
     const int64_t total = (int64_t)bvp_variants(a.mode) * a.n;
-    k_bvp_pass<<<(int)((total + CTR_BVP_BLOCK - 1) / CTR_BVP_BLOCK), CTR_BVP_BLOCK, 0, st>>>(a);
+    static const bool thread_kernel = getenv("CTR_BVP_THREAD_KERNEL") != nullptr;   // A/B switch: one thread per pass (round-2 first form)
+    if (thread_kernel) {
+        k_bvp_pass<<<(int)((total + CTR_BVP_BLOCK - 1) / CTR_BVP_BLOCK), CTR_BVP_BLOCK, 0, st>>>(a);
+    } else {
+        if (!h->bvp_next) CTR_CUDA(cudaMalloc(&h->bvp_next, sizeof(unsigned long long)));
+        CTR_CUDA(cudaMemsetAsync(h->bvp_next, 0, sizeof(unsigned long long), st));
+        a.next = h->bvp_next;
+        const int per_block = (CTR_BLOCK / 32) * 10;     // 3 lanes per pass, 10 passes in flight per warp
+        int64_t grid = (total + per_block - 1) / per_block;
+        const int64_t resident = (int64_t)h->sm_count * CTR_BVP_GMINB;   // persistent: the groups refill themselves from a.next
+        if (grid > resident) grid = resident;
+        if (a.f || (a.mode & 2)) k_bvp_pass_g<true><<<(int)grid, CTR_BLOCK, 0, st>>>(a);
+        else k_bvp_pass_g<false><<<(int)grid, CTR_BLOCK, 0, st>>>(a);
+    }
     h->launches += 1;
     CTR_CUDA(cudaGetLastError());
     return 0;
