@@ -379,8 +379,8 @@ __global__ void __launch_bounds__(CTR_BVP_BLOCK, CTR_BVP_MINB) k_bvp_pass(const 
 // Control flow is warp-synchronous as in fk_dp45: per-pass decisions are predicates, exchanges sit at warp-uniform points.
 // The thread-per-pass kernel above is kept (CTR_BVP_THREAD_KERNEL) as the straight-line statement of the same arithmetic.
 struct BvpLaneSec {
-    double ei, gj, ux, uy;   // own tube on this section (0 when absent / straight)
-    double k;                // ei / gj (0 when absent)
+    double ei, dge, ux, uy;  // own tube on this section: EI, GJ - EI, precurvature (0 when absent / straight)
+    double k;                // EI / GJ (0 when absent)
     double inv_sei;          // 1 / sum of the present tubes' EI
 };
 
@@ -411,7 +411,7 @@ struct BvpLaneTube {       // the lane's own tube and what it needs of the other
 __device__ __forceinline__ void bvp_lane_consts(const BvpLaneTube& T, int pat, int j, BvpLaneSec& c, double& sei) {
     const bool present = (pat >> j) & 1, curved = (pat >> (3 + j)) & 1;
     c.ei = present ? T.ei : 0.0;
-    c.gj = present ? T.gj : 0.0;
+    c.dge = present ? T.gj - T.ei : 0.0;
     c.ux = curved ? T.ux : 0.0;
     c.uy = curved ? T.uy : 0.0;
     c.k = present ? T.k : 0.0;
@@ -419,23 +419,30 @@ __device__ __forceinline__ void bvp_lane_consts(const BvpLaneTube& T, int pat, i
     c.inv_sei = 1.0 / sei;
 }
 
-// S = {u1x, u1y, u_jz, alpha_j, r_j, R_j0, R_j1, R_j2} -> D; fj = the lane's component of the tip force
+// S = {u1x, u1y, u_jz, alpha_j, r_j, R_j0, R_j1, R_j2} -> D; fj = the lane's component of the tip force.
+// The curvature sums of CTR_Model.py:84-112 in factored form.  With u_j = Rz(alpha_j)^T u_1 in xy (:64-73), the seven terms of
+// tube j in du0 collapse (u_jy cos + u_jx sin = u_1y, u_jx cos - u_jy sin = u_1x) to
+//   EI_j (alpha_j' u_1y + u_jz A_j) + (GJ_j - EI_j) u_jz u_1y,   A_j = U_jy cos alpha_j + U_jx sin alpha_j
+// and those in du1 to
+//   EI_j (-alpha_j' u_1x + u_jz B_j) - (GJ_j - EI_j) u_jz u_1x,  B_j = U_jy sin alpha_j - U_jx cos alpha_j,
+// and the twist equation :79 to (EI_j / GJ_j)(u_1x A_j + u_1y B_j): 16 FP64 operations instead of 62.  Same value to ~1e-16
+// relative; the thread-per-pass kernel and oracle/bvp_oracle.c keep the reference's literal expression.
 template <bool LOAD>
 __device__ __forceinline__ void bvp_lane_rhs(const LaneId& id, const BvpLaneSec& c, double fj, const double (&S)[8], double (&D)[8]) {
     __syncwarp();
-    xch_put2(id, 0, S[2], 0.0);                           // u_1z comes from lane 0
+    xch_put2(id, 0, S[2], 0.0);                                // u_1z comes from lane 0
     __syncwarp();
     const double u1z = xch_get2a<double>(id, 0, id.l0);
     double sa = 0.0, ca = 1.0;
     if (id.j != 0) bvp_sincos(S[3], &sa, &ca);                 // alpha_1 (relative to tube 1) is identically 0
-    const double ux = ca * S[0] + sa * S[1], uy = -sa * S[0] + ca * S[1], uz = S[2];   // u_j = Rz(alpha_j)^T u_1 (:64-73)
-    const bool on = c.gj != 0.0;
-    D[2] = on ? c.k * (ux * c.uy - uy * c.ux) : 0.0;                          // :76-82
+    const double uz = S[2];
+    const double A = fma(ca, c.uy, sa * c.ux), B = fma(sa, c.uy, -(ca * c.ux));
+    const bool on = c.ei != 0.0;
+    D[2] = on ? c.k * fma(S[0], A, S[1] * B) : 0.0;            // :76-82
     D[3] = on ? S[2] - u1z : 0.0;
-    double p0 = D[3] * c.ei * S[1] + c.uy * c.ei * uz * ca + c.ux * c.ei * uz * sa - c.ei * uy * uz * ca + c.gj * uy * uz * ca -
-                c.ei * ux * uz * sa + c.gj * ux * uz * sa;                              // :84-112, this tube's terms
-    double p1 = -D[3] * c.ei * S[0] + c.uy * c.ei * uz * sa - c.ux * c.ei * uz * ca + c.ei * ux * uz * ca - c.gj * ux * uz * ca -
-                c.ei * uy * uz * sa + c.gj * uy * uz * sa;
+    const double w = c.dge * uz;
+    double p0 = fma(w, S[1], c.ei * fma(uz, A, D[3] * S[1]));
+    double p1 = fma(-w, S[0], c.ei * fma(uz, B, -(D[3] * S[0])));
     group_sum2(id, p0, p1);
     double g0 = 0.0, g1 = 0.0;
     if (LOAD) {                                                // R^T f: rows are spread over the lanes
@@ -443,12 +450,12 @@ __device__ __forceinline__ void bvp_lane_rhs(const LaneId& id, const BvpLaneSec&
         g1 = S[6] * fj;
         group_sum2(id, g0, g1);
     }
-    D[0] = -p0 * c.inv_sei + g1 * c.inv_sei;                   // :114-118
-    D[1] = -p1 * c.inv_sei - g0 * c.inv_sei;
+    D[0] = (g1 - p0) * c.inv_sei;                              // :114-118
+    D[1] = -(p1 + g0) * c.inv_sei;
     D[4] = S[7];                                               // r' = R e3
-    D[5] = S[6] * u1z - S[7] * S[1];                           // R' = R u_hat(u_1), row j
-    D[6] = S[7] * S[0] - S[5] * u1z;
-    D[7] = S[5] * S[1] - S[6] * S[0];
+    D[5] = fma(S[6], u1z, -(S[7] * S[1]));                     // R' = R u_hat(u_1), row j
+    D[6] = fma(S[7], S[0], -(S[5] * u1z));
+    D[7] = fma(S[5], S[1], -(S[6] * S[0]));
 }
 
 // sum over the 20 states of (x / scale)^2: lane 0 counts its 8 values, lanes 1 / 2 their 6 own ones (u1x, u1y are replicated)
@@ -562,7 +569,7 @@ __device__ __forceinline__ void bvp_fetch(const BvpArgs& a, int j, int64_t p, Gr
     s.dtip = pick3(j, L[0] + q[0], L[1] + q[1], L[2] + q[2]);
     s.best = CUDART_INF;                                       // :231-235 for the lane's own tube (lanes 1, 2)
     s.uz_tip = 0.0;
-    s.c.ei = s.c.gj = s.c.ux = s.c.uy = s.c.k = s.c.inv_sei = 0.0;
+    s.c.ei = s.c.dge = s.c.ux = s.c.uy = s.c.k = s.c.inv_sei = 0.0;
     s.ksec = 0;
     s.steps = 0;
     s.t = s.tf = s.h_abs = 0.0;
@@ -617,7 +624,7 @@ __global__ void __launch_bounds__(CTR_BLOCK, CTR_BVP_GMINB) k_bvp_pass_g(const B
     BvpLaneState s;
 #pragma unroll
     for (int i = 0; i < 8; ++i) s.y[i] = s.fv[i] = 0.0;
-    s.c.ei = s.c.gj = s.c.ux = s.c.uy = s.c.k = s.c.inv_sei = 0.0;
+    s.c.ei = s.c.dge = s.c.ux = s.c.uy = s.c.k = s.c.inv_sei = 0.0;
     s.T.ei = s.T.gj = s.T.ux = s.T.uy = s.T.k = s.T.EI[0] = s.T.EI[1] = s.T.EI[2] = 0.0;
     s.fj = s.dtip = s.best = s.uz_tip = s.t = s.tf = s.h_abs = 0.0;
     s.p = 0;
@@ -682,7 +689,7 @@ __global__ void __launch_bounds__(CTR_BLOCK, CTR_BVP_GMINB) k_bvp_pass_g(const B
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 if (init) s.fv[i] = D[i];
-                rs[i] = rcp_fast(atol + fabs(s.y[i]) * rtol);
+                rs[i] = rcp_fast(fma(fabs(s.y[i]), rtol, atol));
             }
             if (init) {                                        // s.t[0] of the section is a stored point too
                 const double dist = fabs(s.t - s.dtip);
@@ -693,20 +700,21 @@ __global__ void __launch_bounds__(CTR_BLOCK, CTR_BVP_GMINB) k_bvp_pass_g(const B
             }
             double p0 = bvp_lane_sq(j, s.y, rs), p1 = bvp_lane_sq(j, D, rs);
             group_sum2(id, p0, p1);
-            const double d0 = sqrt(p0 / NB), d1 = sqrt(p1 / NB);
+            const double m0 = p0 * (1.0 / NB), m1 = p1 * (1.0 / NB);                   // d0^2, d1^2 of common.py:105-108
             const double interval = fabs(s.tf - s.t);
-            double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
-            h0 = fmin(h0, interval);
+            double h0 = (m0 < 1e-10 || m1 < 1e-10) ? 1e-6 : 0.01 * sqrt_fast(m0 * rcp_fast(m1));
+            h0 = dmin(h0, interval);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) Y[i] = s.y[i] + h0 * D[i];
+            for (int i = 0; i < 8; ++i) Y[i] = fma(h0, D[i], s.y[i]);
             bvp_lane_rhs<LOAD>(id, s.c, s.fj, Y, D1);
 #pragma unroll
             for (int i = 0; i < 8; ++i) D1[i] = D1[i] - D[i];
             double p2 = bvp_lane_sq(j, D1, rs), dummy = 0.0;
             group_sum2(id, p2, dummy);
-            const double d2 = sqrt(p2 / NB) / h0;
-            const double h1 = (d1 <= 1e-15 && d2 <= 1e-15) ? fmax(1e-6, h0 * 1e-3) : pow_m13(fmax(d1, d2) * 100.0);
-            if (init) s.h_abs = fmin(fmin(100 * h0, h1), fmin(interval, max_step));
+            const double m2 = p2 * (1.0 / NB) * rcp_fast(h0 * h0);                        // d2^2
+            const double mx = dmax(m1, m2);
+            const double h1 = (mx <= 1e-30) ? dmax(1e-6, h0 * 1e-3) : pow_m13(100.0 * sqrt_fast(mx));   // (0.01 / max(d1, d2))^(1/3)
+            if (init) s.h_abs = dmin(dmin(100 * h0, h1), dmin(interval, max_step));
         }
         // ---- one step attempt (rk.py _step_impl, RK23 tableau)
         const double min_step = 10 * fabs(nextafter(s.t, CUDART_INF) - s.t);
@@ -721,26 +729,27 @@ __global__ void __launch_bounds__(CTR_BLOCK, CTR_BVP_GMINB) k_bvp_pass_g(const B
         const double h_try = fabs(h);
         double k2[8], k3[8], k4[8], yn[8], Y[8], ep[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) Y[i] = s.y[i] + (s.fv[i] * 0.5) * h;
+        for (int i = 0; i < 8; ++i) Y[i] = fma(s.fv[i] * 0.5, h, s.y[i]);
         bvp_lane_rhs<LOAD>(id, s.c, s.fj, Y, k2);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) Y[i] = s.y[i] + (s.fv[i] * 0.0 + k2[i] * 0.75) * h;
+        for (int i = 0; i < 8; ++i) Y[i] = fma(k2[i] * 0.75, h, s.y[i]);
         bvp_lane_rhs<LOAD>(id, s.c, s.fj, Y, k3);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            yn[i] = s.y[i] + h * (s.fv[i] * (2.0 / 9) + k2[i] * (1.0 / 3) + k3[i] * (4.0 / 9));
-            ep[i] = s.fv[i] * (5.0 / 72) + k2[i] * (-1.0 / 12) + k3[i] * (-1.0 / 9);   // k2, k3 end here: 16 registers fewer across the last stage
+            yn[i] = fma(h, fma(k3[i], 4.0 / 9, fma(k2[i], 1.0 / 3, s.fv[i] * (2.0 / 9))), s.y[i]);
+            ep[i] = fma(k3[i], -1.0 / 9, fma(k2[i], -1.0 / 12, s.fv[i] * (5.0 / 72)));   // k2, k3 end here: 16 registers fewer across the last stage
         }
         bvp_lane_rhs<LOAD>(id, s.c, s.fj, yn, k4);
         double pe = 0.0, dummy = 0.0;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const double sc = atol + fabs(absmax_arg(s.y[i], yn[i])) * rtol;
-            const double e = (ep[i] + k4[i] * (1.0 / 8)) * h * rcp_fast(sc);   // a zero numerator sends '/' down its slow path
+            const double sc = fma(fabs(absmax_arg(s.y[i], yn[i])), rtol, atol);
+            const double e = fma(k4[i], 1.0 / 8, ep[i]) * h * rcp_fast(sc);   // a zero numerator sends '/' down its slow path
             if (i >= 2 || j == 0) pe = fma(e, e, pe);
         }
         group_sum2(id, pe, dummy);
-        const double err = sqrt(pe / NB);
+        const double me = pe * (1.0 / NB);
+        const double err = me > 1e-200 ? sqrt_fast(me) : 0.0;       // below: the controller saturates at factor 10 long before
         const double fac = 0.9 * pow_m13(err);
         if (!s.done) {
             s.h_abs = h_try;
@@ -748,8 +757,8 @@ __global__ void __launch_bounds__(CTR_BLOCK, CTR_BVP_GMINB) k_bvp_pass_g(const B
                 s.failed = true;
                 s.done = true;
             } else if (err < 1.0) {
-                double factor = (err == 0.0) ? 10.0 : fmin(10.0, fac);
-                if (s.rejected) factor = fmin(1.0, factor);
+                double factor = (err == 0.0) ? 10.0 : dmin(10.0, fac);
+                if (s.rejected) factor = dmin(1.0, factor);
                 s.h_abs *= factor;
                 s.t = t_new;
 #pragma unroll
@@ -770,7 +779,7 @@ __global__ void __launch_bounds__(CTR_BLOCK, CTR_BVP_GMINB) k_bvp_pass_g(const B
                     s.failed = true;
                     s.done = true;
                 }
-                s.h_abs *= fmax(0.2, fac);
+                s.h_abs *= dmax(0.2, fac);
                 s.rejected = true;
             }
             if (s.steps > 100000) {
