@@ -620,8 +620,8 @@ def kernel_table(args, dev, pool, fma_peak, hbm_peak):
     steps_b = float(e.bvp_pass(qb)['steps'].double().sum())
     # algorithmic flops: RK23 = 3 RHS per attempt (+2 per section start), RHS of the 20-state model ~ 330 flop (6 sincos, the
     # two curvature sums of CTR_Model.py:84-112, R u_hat), + 20 x 12 for the stage combinations and the error norm
-    fma_row("k_bvp_pass (RK23, 20 states)", sec, steps_b * (3 * 330.0 + 240.0),
-            "%d configs, %.0f accepted steps each; one thread per pass, state in local memory" % (nb, steps_b / nb))
+    fma_row("k_bvp_pass_g (RK23, 20 states)", sec, steps_b * (3 * 330.0 + 240.0),
+            "%d configs, %.0f accepted steps each; 3 lanes per pass, state in registers, groups refill themselves from a work counter" % (nb, steps_b / nb))
     sec = timed(lambda: e.bvp_jacobian(qb[:32768], compliance=False), reps=3, warm=1)
     fma_row("ctr_bvp_jacobian (7 passes)", sec, 7.0 * steps_b / nb * 32768 * (3 * 330.0 + 240.0), "32768 configs = 229376 passes")
     e.close()

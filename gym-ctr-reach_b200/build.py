@@ -5,7 +5,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, 'csrc', 'ctr_kernels.cu')
-DEPS = [SRC, os.path.join(HERE, 'csrc', 'ctr_device.cuh'), os.path.join(HERE, 'csrc', 'ctr_her.cuh'), os.path.join(HERE, 'csrc', 'ctr_ik.cuh'), os.path.join(HERE, '..', 'include', 'ctr_b200.h')]
+DEPS = sorted(os.path.join(HERE, 'csrc', f) for f in os.listdir(os.path.join(HERE, 'csrc'))) + [os.path.join(HERE, '..', 'include', 'ctr_b200.h')]
 OUT = os.path.join(HERE, 'libctr_b200.so')
 NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 # -fmad=false: every FMA of the kernels is an explicit fma(); implicit contraction is off so that all instantiations of the
