@@ -749,7 +749,7 @@ __global__ void __launch_bounds__(CTR_BLOCK, CTR_BVP_GMINB) k_bvp_pass_g(const B
         }
         group_sum2(id, pe, dummy);
         const double me = pe * (1.0 / NB);
-        const double err = me > 1e-200 ? sqrt_fast(me) : 0.0;       // below: the controller saturates at factor 10 long before
+        const double err = !(me <= 1e-200) ? sqrt_fast(me) : 0.0;   // below: the controller saturates at factor 10 long before; a NaN stays a NaN
         const double fac = 0.9 * pow_m13(err);
         if (!s.done) {
             s.h_abs = h_try;

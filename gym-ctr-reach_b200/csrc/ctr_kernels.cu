@@ -1012,7 +1012,8 @@ struct ctr_handle {
     void* stage_fk_dev;
     size_t bvp_cap;            // ctr_bvp_* scratch (bytes)
     void* bvp_dev;
-    unsigned long long* bvp_next;   // work counter of k_bvp_pass_g
+    unsigned long long* bvp_next;   // work counters of k_bvp_pass_g (ring of 64)
+    unsigned bvp_launches;
     int64_t ik_cap;            // ctr_jacobian / ctr_ik_dls scratch: joints f64 [6][7n] | tips f64 [3][7n] | system i32 [7n] | frozen u8 [n] | active i32
     void* ik_dev;
 };
@@ -1220,6 +1221,7 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     h->bvp_cap = 0;
     h->bvp_dev = nullptr;
     h->bvp_next = nullptr;
+    h->bvp_launches = 0;
     cudaDeviceProp prop;
     CTR_CUDA(cudaGetDeviceProperties(&prop, device));
     h->sm_count = prop.multiProcessorCount;
@@ -2299,9 +2301,10 @@ static int bvp_launch(ctr_handle* h, const BvpArgs& a_in, cudaStream_t st) {
     if (thread_kernel) {
         k_bvp_pass<<<(int)((total + CTR_BVP_BLOCK - 1) / CTR_BVP_BLOCK), CTR_BVP_BLOCK, 0, st>>>(a);
     } else {
-        if (!h->bvp_next) CTR_CUDA(cudaMalloc(&h->bvp_next, sizeof(unsigned long long)));
-        CTR_CUDA(cudaMemsetAsync(h->bvp_next, 0, sizeof(unsigned long long), st));
-        a.next = h->bvp_next;
+        // work counters: a ring of 64, one per launch, so that launches the caller runs on different streams do not share one
+        if (!h->bvp_next) CTR_CUDA(cudaMalloc(&h->bvp_next, 64 * sizeof(unsigned long long)));
+        a.next = h->bvp_next + (h->bvp_launches++ & 63);
+        CTR_CUDA(cudaMemsetAsync(a.next, 0, sizeof(unsigned long long), st));
         const int per_block = (CTR_BLOCK / 32) * 10;     // 3 lanes per pass, 10 passes in flight per warp
         int64_t grid = (total + per_block - 1) / per_block;
         const int64_t resident = (int64_t)h->sm_count * CTR_BVP_GMINB;   // persistent: the groups refill themselves from a.next

@@ -148,3 +148,37 @@ def test_dls_controller_on_the_bvp_model_vs_oracle(oracle_c, oracle_py, vec_fact
         if it + 1 == iters[i] and np.abs(qq - q[i]).max() < 1e-6:
             agree += 1
     assert agree >= 0.9 * len(range(0, n, 8)), agree
+
+
+@pytest.mark.gpu
+def test_bvp_pass_is_independent_of_batch_shape_and_isolates_failed_rows(bvp, vec_factory):
+    """The lane-group kernel hands passes to whichever group is free: a row's result must not depend on the batch it is in
+    (1 row, a partial warp, partial blocks, more rows than resident groups), and a row that cannot be integrated (NaN joint)
+    comes back as NaN / steps -1 and is counted, without touching its neighbours."""
+    import torch
+    env = vec_factory(16, select_systems=[0, 1, 2, 3])
+    sel = np.nonzero(bvp['pass_tol'] == 0.01)[0]
+    q, f, u, sysid = bvp['pass_q'][sel], bvp['pass_f'][sel], bvp['pass_u'][sel], bvp['pass_system'][sel].astype(np.int32)
+    full = env.bvp_pass(q, force=f, u_init=u, system=sysid)
+    full = {k: v.cpu().numpy() for k, v in full.items()}
+    for n in (1, 7, 11, 41, 333):
+        part = env.bvp_pass(q[:n], force=f[:n], u_init=u[:n], system=sysid[:n])
+        for k in ('tip', 'R', 'cost', 'steps'):
+            assert np.array_equal(part[k].cpu().numpy(), full[k][:n]), (n, k)
+    reps = 40                                                       # 40 x 512 rows: more passes than resident lane groups (148 x 3 x 40)
+    big = env.bvp_pass(np.tile(q, (reps, 1)), force=np.tile(f, (reps, 1)), u_init=np.tile(u, (reps, 1)), system=np.tile(sysid, reps))
+    for k in ('tip', 'cost', 'steps'):
+        got = big[k].cpu().numpy().reshape((reps, len(sel)) + full[k].shape[1:])
+        assert all(np.array_equal(got[r], full[k]) for r in range(reps)), k
+    before = env.fault_counters()['fk_failed']
+    qb = q[:64].copy()
+    qb[5, 4] = np.nan
+    qb[33, 3] = np.nan
+    out = env.bvp_pass(qb, force=f[:64], u_init=u[:64], system=sysid[:64])
+    steps, tip = out['steps'].cpu().numpy(), out['tip'].cpu().numpy()
+    torch.cuda.synchronize()
+    bad = np.zeros(64, dtype=bool)
+    bad[[5, 33]] = True
+    assert np.all(steps[bad] == -1) and np.all(np.isnan(tip[bad]))
+    assert np.array_equal(steps[~bad], full['steps'][:64][~bad]) and np.array_equal(tip[~bad], full['tip'][:64][~bad])
+    assert env.fault_counters()['fk_failed'] - before == 2
