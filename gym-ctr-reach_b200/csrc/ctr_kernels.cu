@@ -10,6 +10,7 @@
 //   k_mask_to_list         compaction of an explicit reset mask
 #include <cuda_runtime.h>
 #include <chrono>
+#include <mutex>
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -1178,6 +1179,8 @@ extern "C" {
 const char* ctr_last_error(void) { return g_err.c_str(); }
 int ctr_abi_version(void) { return CTR_ABI_VERSION; }
 
+static cudaError_t jacobian_scratch_resolve(int device, void** out);   // ctr_jacobian_noalloc, below
+
 int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle** out) {
     if (!cfg || !out) CTR_FAIL("null argument");
     if (cfg->abi_version != CTR_ABI_VERSION) CTR_FAIL("ctr_config.abi_version mismatch");
@@ -1222,6 +1225,7 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     h->bvp_dev = nullptr;
     h->bvp_next = nullptr;
     h->bvp_launches = 0;
+    jacobian_scratch_resolve(h->device, nullptr);   // ctr_jacobian_noalloc: device address of its static scratch, once per device (its error, if any, is reported by that call)
     cudaDeviceProp prop;
     CTR_CUDA(cudaGetDeviceProperties(&prop, device));
     h->sm_count = prop.multiProcessorCount;
@@ -2218,6 +2222,66 @@ int ctr_jacobian(ctr_handle* h, const double* joints_dev, const int32_t* system_
     IkScratch sc;
     int rc = ik_scratch(h, n, &sc);
     if (!rc) rc = ik_systems(sc, system_dev, n, st);
+    if (!rc) rc = ik_solve7(h, sc, joints_dev, system_dev, n, eps, st);
+    if (rc) return rc;
+    k_ik_jacobian<<<(int)((n + 255) / 256), 256, 0, st>>>(sc.tips, n, eps, J_dev, tip_dev);
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---- ctr_jacobian_noalloc: ctr_jacobian for callers that cannot call cudaMalloc (graph capture, serving loops) ---------------
+// No counterpart in the reference.  The 7n perturbed joint columns, their 7n
+// tips and the 7n system ids live in ONE file-scope device array instead of the handle's grow-on-demand allocation.  Every
+// GPU that loads the library holds the array (CTR_JACOBIAN_NOALLOC_MAX * 532 B = 8.3 MiB) until the process exits.  Every
+// call on a device shares it: calls that overlap on the GPU (different streams, different handles of one device) race.
+// Nothing in it has to start at zero -- k_ik_perturb writes all 42n joint values, the system copies all 7n ids and k_fk all 21n
+// tip values (NaN for a failed solve) before k_ik_jacobian reads them -- so the previous call's contents are never seen.
+constexpr int64_t NOALLOC_BYTES_PER_CONFIG = 7 * 6 * 8 + 7 * 3 * 8 + 7 * 4;
+static __device__ __align__(256) unsigned char g_jacobian_scratch[CTR_JACOBIAN_NOALLOC_MAX * NOALLOC_BYTES_PER_CONFIG];
+// In host code `g_jacobian_scratch` is only a stand-in for the symbol: its device address is resolved once per device, with
+// that device current (ctr_create does it at set-up; the entry point itself for a device no handle was created on).
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static void* g_jacobian_scratch_addr[NOALLOC_MAX_DEVICES];
+static cudaError_t g_jacobian_scratch_err[NOALLOC_MAX_DEVICES];
+static bool g_jacobian_scratch_known[NOALLOC_MAX_DEVICES];
+static std::mutex g_jacobian_scratch_mutex;
+static cudaError_t jacobian_scratch_resolve(int device, void** out) {      // the caller has made `device` current
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_jacobian_scratch_mutex);
+    if (!g_jacobian_scratch_known[device]) {
+        void* ptr = nullptr;
+        g_jacobian_scratch_err[device] = cudaGetSymbolAddress((void**)&ptr, g_jacobian_scratch);
+        g_jacobian_scratch_addr[device] = g_jacobian_scratch_err[device] == cudaSuccess ? ptr : nullptr;
+        g_jacobian_scratch_known[device] = true;
+    }
+    if (out) *out = g_jacobian_scratch_addr[device];
+    return g_jacobian_scratch_err[device];
+}
+
+int ctr_jacobian_noalloc(ctr_handle* h, const double* joints_dev, const int32_t* system_dev, int64_t n, double eps, double* J_dev,
+                         double* tip_dev, void* stream) {
+    if (!h || !joints_dev || !J_dev) CTR_FAIL("null argument");
+    if (!(eps > 0.0)) CTR_FAIL("eps must be > 0");
+    if (n <= 0) return 0;
+    if (n > CTR_JACOBIAN_NOALLOC_MAX)
+        CTR_FAIL("ctr_jacobian_noalloc: n exceeds CTR_JACOBIAN_NOALLOC_MAX (16384 configurations, the size of the static device "
+                 "scratch array); split the batch or call ctr_jacobian");
+    CTR_CUDA(cudaSetDevice(h->device));
+    void* base = nullptr;
+    const cudaError_t err = jacobian_scratch_resolve(h->device, &base);
+    if (err != cudaSuccess || !base) {
+        g_err = std::string("ctr_jacobian_noalloc: cudaGetSymbolAddress of the static scratch array failed: ") + cudaGetErrorString(err);
+        return 2;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    IkScratch sc;                                   // compact layout for this n: joints f64 [6][7n] | tips f64 [3][7n] | system i32 [7n]
+    sc.block = (double*)base;
+    sc.tips = sc.block + 42 * n;
+    sc.system = (int32_t*)(sc.tips + 21 * n);
+    sc.active = nullptr;
+    sc.frozen = nullptr;
+    int rc = ik_systems(sc, system_dev, n, st);
     if (!rc) rc = ik_solve7(h, sc, joints_dev, system_dev, n, eps, st);
     if (rc) return rc;
     k_ik_jacobian<<<(int)((n + 255) / 256), 256, 0, st>>>(sc.tips, n, eps, J_dev, tip_dev);

@@ -27,7 +27,7 @@ EXPORTS = ['ctr_last_error', 'ctr_abi_version', 'ctr_create', 'ctr_destroy', 'ct
            'ctr_step_host', 'ctr_step_host_packed', 'ctr_step_host_packed_f32', 'ctr_step_host_delta', 'ctr_reset_host', 'ctr_compute_reward', 'ctr_relabel', 'ctr_stats', 'ctr_stats_reset',
            'ctr_launch_count', 'ctr_work_counters', 'ctr_fault_counters', 'ctr_debug_buffer', 'ctr_segment_tables', 'ctr_checkpoint_bytes', 'ctr_checkpoint_save',
            'ctr_checkpoint_load', 'ctr_measure_fma_peak', 'ctr_her_begin', 'ctr_her_store',
-           'ctr_her_sample', 'ctr_fk_shape', 'ctr_jacobian', 'ctr_ik_dls', 'ctr_bvp_pass', 'ctr_bvp_jacobian', 'ctr_bvp_solve',
+           'ctr_her_sample', 'ctr_fk_shape', 'ctr_jacobian', 'ctr_jacobian_noalloc', 'ctr_ik_dls', 'ctr_bvp_pass', 'ctr_bvp_jacobian', 'ctr_bvp_solve',
            'ctr_bvp_ik_dls']
 
 
@@ -134,6 +134,7 @@ def load():
     lib.ctr_launch_count.argtypes = [vp]
     lib.ctr_fk_shape.argtypes = [vp, vp, vp, vp, i64, i32, vp, vp, vp, vp, vp]
     lib.ctr_jacobian.argtypes = [vp, vp, vp, i64, f64, vp, vp, vp]
+    lib.ctr_jacobian_noalloc.argtypes = [vp, vp, vp, i64, f64, vp, vp, vp]
     lib.ctr_ik_dls.argtypes = [vp, vp, vp, vp, i64, f64, f64, f64, i32, vp, vp, vp]
     lib.ctr_bvp_pass.argtypes = [vp, vp, vp, vp, vp, vp, i64, f64, vp, vp, vp, vp, vp]
     lib.ctr_bvp_jacobian.argtypes = [vp, vp, vp, vp, vp, vp, i64, f64, vp, vp, vp, vp]

@@ -298,6 +298,22 @@ class CtrReachVecEnv(object):
                                          self._stream()))
         return J.t().reshape(n, 3, 6), tip.t()
 
+    JACOBIAN_NOALLOC_MAX = 16384          # CTR_JACOBIAN_NOALLOC_MAX of include/ctr_b200.h
+
+    def jacobian_noalloc(self, joints_soa, J_out, tip_out=None, system=None, eps=1e-4):
+        """ctr_jacobian_noalloc: the Jacobian for callers that may not allocate (no counterpart in the reference).  Everything
+        is the caller's: joints_soa float64 [6][n], J_out float64 [18][n], tip_out float64 [3][n] or None, system int32 [n]
+        or None, all contiguous on this env's device.  The scratch is a static device array of the library shared by every
+        call on the device (n <= JACOBIAN_NOALLOC_MAX; overlapping calls race).  No torch allocation happens here either."""
+        n = joints_soa.shape[1]
+        for t, rows, dt in ((joints_soa, 6, torch.float64), (J_out, 18, torch.float64), (tip_out, 3, torch.float64)):
+            if t is not None and not (t.is_cuda and t.dtype == dt and t.is_contiguous() and tuple(t.shape) == (rows, n)):
+                raise ValueError("jacobian_noalloc takes contiguous device tensors of shape (%d, n), %s" % (rows, dt))
+        if system is not None and not (system.is_cuda and system.dtype == torch.int32 and system.is_contiguous() and system.numel() == n):
+            raise ValueError("system must be a contiguous int32 device tensor of n elements")
+        _lib.check(self.lib.ctr_jacobian_noalloc(self.handle, _lib.ptr(joints_soa), _lib.ptr(system), n, float(eps), _lib.ptr(J_out),
+                                                 _lib.ptr(tip_out), self._stream()))
+
     def ik_dls(self, target, q0, system=None, lam=0.25, eps=1e-4, tol=1e-3, max_iters=500):
         """Damped-least-squares position IK of the reference's baseline controller (src/jacobian_controller.py:19-73), batched:
         target (n, 3), q0 (n, 6) -> q (n, 6), err (n,), iters (n,).  Joints are not clipped (the reference does not)."""

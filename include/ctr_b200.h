@@ -258,6 +258,22 @@ int ctr_jacobian(ctr_handle *h, const double *joints_dev, const int32_t *system_
 int ctr_ik_dls(ctr_handle *h, const double *target_dev, double *joints_dev, const int32_t *system_dev, int64_t n, double lam,
                double eps, double tol, int32_t max_iters, double *err_dev, int32_t *iters_dev, void *stream);
 
+/* ---- ctr_jacobian without any allocation ----------------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, same kernels and same
+ * results as ctr_jacobian, but the scratch of the 7n solves (perturbed joints, tips, system ids: 532 B per configuration)
+ * is a file-scope static __device__ array of the library instead of the handle's grow-on-demand cudaMalloc, and the call
+ * performs no cudaMalloc / cudaFree / allocating library call.
+ *  - n > CTR_JACOBIAN_NOALLOC_MAX is rejected (return code 1, ctr_last_error says so); split the batch or use ctr_jacobian.
+ *  - every GPU that loads the library holds the array (CTR_JACOBIAN_NOALLOC_MAX * 532 B = 8.3 MiB) until the process exits.
+ *  - ALL calls on one device share the array, whatever the handle or stream: calls that overlap on the GPU race.  Calls
+ *    on one stream are ordered and safe.  The array keeps the last call's contents; nothing in it has to start at zero
+ *    (every value read is written earlier in the same call), so nothing is cleared.
+ *  - the caller passes device inputs and outputs as for ctr_jacobian; the launches go to `stream`, nothing synchronises. */
+#define CTR_JACOBIAN_NOALLOC_MAX 16384
+int ctr_jacobian_noalloc(ctr_handle *h, const double *joints_dev, const int32_t *system_dev, int64_t n, double eps, double *J_dev,
+                         double *tip_dev, void *stream);
+
 /* ---- the reference's full model with tip load (CTR_Python/CTR_Model.py) as a second kinematics back-end
  * State of the model: u1x u1y | u1z u2z u3z | twist angles relative to tube 1 | r | R (20 values, ode_eq :56-128), integrated
  * section by section with scipy's RK23 and max_step (ode_solver :130-236).  All arrays are SoA f64 [rows][n].
