@@ -295,6 +295,7 @@ __device__ __forceinline__ double shape_abscissa(int i, double a, double step, d
     return (i == SHAPE_SAMPLES - 1) ? b : __dadd_rn(__dmul_rn((double)i, step), a);
 }
 
+
 template <typename T> __device__ __forceinline__ T dpc(int i);
 template <> __device__ __forceinline__ double dpc<double>(int i) { return c_dp64[i]; }
 template <> __device__ __forceinline__ float dpc<float>(int i) { return c_dp32[i]; }
@@ -387,6 +388,78 @@ __device__ __forceinline__ void build_sections(const double* L, const double* Lc
     }
     if (writer) gs.nsec = m | (skipped << 8);
     if (SYNC) __syncwarp();
+}
+
+// The dense-output samples are not evaluated inside the divergent accept branch (a warp would run that loop for the largest
+// number of samples any of its lanes' steps covers, every pass: 60 % of the instructions of the first form of k_fk_shape).
+// An accepted step only LOGS what its interpolant needs -- t_old, t_new, r_j(t_old), Q = K^T P for r_j and 1 / h, 8 doubles -- in a
+// per-lane log (local memory, SHAPE_LOG_CAP steps); the samples are evaluated afterwards in one warp-uniform loop in which every
+// lane walks its own log and its own abscissae (shape_flush: when some lane's log is full and after the last step), so the trip
+// count is the largest number of samples + steps of a LANE, not the sum over the passes of the largest per-step count.
+constexpr int SHAPE_LOG_CAP = 24;
+constexpr int SHAPE_LOG_W = 8;
+struct ShapeCursor {
+    int sec, i;        // next sample to evaluate: abscissa i of section sec
+    int n;             // steps in the log
+};
+template <bool ON>
+struct ShapeLog {
+    double e[ON ? SHAPE_LOG_CAP * SHAPE_LOG_W : 1];
+};
+template <bool ON>
+__device__ __forceinline__ void shape_flush(const GroupScratch& gs, int nsec, const ShapeOut& shape, ShapeLog<ON>& lg, ShapeCursor& cur) {
+    int s = -1;                                                                  // log entry held in registers
+    double a = 0.0, b = 0.0, step = 0.0, te = 0.0;
+    double t_old = 0.0, t_new = -1e300, h_d = 0.0, inv_h = 0.0, y_old = 0.0, q0 = 0.0, q1 = 0.0, q2 = 0.0, q3 = 0.0;
+    bool have_sec = false;
+    double* out = shape.base + (int64_t)(cur.sec * SHAPE_SAMPLES + cur.i) * shape.stride;
+    int pt = cur.sec * SHAPE_SAMPLES + cur.i;
+    // every iteration either evaluates the lane's next sample or takes its next step from the log
+    while (__any_sync(FULL, s < cur.n)) {
+        if (s < cur.n) {
+            if (!have_sec && cur.sec < nsec) {                                   // abscissae of the section the cursor is in (none after the last)
+                a = gs.t0[cur.sec];
+                b = gs.tf[cur.sec];
+                step = __ddiv_rn(__dsub_rn(b, a), (double)(SHAPE_SAMPLES - 1));
+                te = shape_abscissa(cur.i, a, step, b);
+                have_sec = true;
+            }
+            if (have_sec && te <= t_new) {                                       // ivp.py: searchsorted(t_eval, t, 'right')
+                const double x = __dmul_rn(__dsub_rn(te, t_old), inv_h);         // differs from numpy's (te - t) / h by <= 1 ulp
+                const double x2 = __dmul_rn(x, x), x3 = __dmul_rn(x2, x), x4 = __dmul_rn(x3, x);   // np.cumprod
+                double acc = __dmul_rn(q0, x);
+                acc = __dadd_rn(acc, __dmul_rn(q1, x2));
+                acc = __dadd_rn(acc, __dmul_rn(q2, x3));
+                acc = __dadd_rn(acc, __dmul_rn(q3, x4));
+                if (pt < shape.max_pts) *out = __dadd_rn(__dmul_rn(h_d, acc), y_old);
+                out += shape.stride;
+                pt += 1;
+                cur.i += 1;
+                if (cur.i == SHAPE_SAMPLES) {
+                    cur.i = 0;
+                    cur.sec += 1;
+                    have_sec = false;
+                } else {
+                    te = shape_abscissa(cur.i, a, step, b);
+                }
+            } else {                                                             // next step of the log
+                s += 1;
+                if (s < cur.n) {
+                    const double* L = lg.e + s * SHAPE_LOG_W;
+                    t_old = L[0];
+                    t_new = L[1];
+                    y_old = L[2];
+                    q0 = L[3];
+                    q1 = L[4];
+                    q2 = L[5];
+                    q3 = L[6];
+                    inv_h = L[7];
+                    h_d = t_new - t_old;
+                }
+            }
+        }
+    }
+    cur.n = 0;
 }
 
 // ---- per-section constants in the lane-rotated form -----------------------------------------------------------
@@ -554,8 +627,9 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
     double t = 0.0, tf = 0.0, h_abs = 0.0;
     bool done = !valid, need_sec = true, rejected = false, failed = false;
     bool first = true;   // warp-uniform: no RHS has been evaluated yet, so slot 0 needs the trigonometry
-    int sh_i = SHAPE_SAMPLES, sh_sec = -1;          // SHAPE: next abscissa of the current section, sections started
-    double sh_a = 0.0, sh_step = 0.0;
+    int sh_sec = -1;                                // SHAPE: sections started
+    ShapeLog<SHAPE> sh_log;
+    ShapeCursor sh_cur{0, 0, 0};
     info.shape_secs = 0;
 
     for (;;) {
@@ -566,12 +640,7 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
                 if (init) {
                     need_sec = false;
                     rejected = false;
-                    if (SHAPE) {
-                        sh_a = t;
-                        sh_step = __ddiv_rn(__dsub_rn(tf, t), (double)(SHAPE_SAMPLES - 1));
-                        sh_i = 0;
-                        sh_sec += 1;
-                    }
+                    if (SHAPE) sh_sec += 1;
                 }
             }
         }
@@ -703,20 +772,16 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
                         q = __dadd_rn(q, __dmul_rn((double)k6[2], c_dpP[20 + pw]));
                         Q[pw] = __dadd_rn(q, __dmul_rn((double)k7[2], c_dpP[24 + pw]));
                     }
-                    const double inv_h = __ddiv_rn(1.0, h_d);   // one division per accepted step; x differs from numpy's (te - t) / h by <= 1 ulp
-                    while (sh_i < SHAPE_SAMPLES) {
-                        const double te = shape_abscissa(sh_i, sh_a, sh_step, tf);
-                        if (!(te <= t_new)) break;                                  // ivp.py: searchsorted(t_eval, t, 'right')
-                        const double x = __dmul_rn(__dsub_rn(te, t), inv_h);
-                        const double x2 = __dmul_rn(x, x), x3 = __dmul_rn(x2, x), x4 = __dmul_rn(x3, x);   // np.cumprod
-                        double acc = __dmul_rn(Q[0], x);
-                        acc = __dadd_rn(acc, __dmul_rn(Q[1], x2));
-                        acc = __dadd_rn(acc, __dmul_rn(Q[2], x3));
-                        acc = __dadd_rn(acc, __dmul_rn(Q[3], x4));
-                        const int pt = sh_sec * SHAPE_SAMPLES + sh_i;
-                        if (pt < shape.max_pts) shape.base[(int64_t)pt * shape.stride] = __dadd_rn(__dmul_rn(h_d, acc), (double)y[2]);
-                        sh_i += 1;
-                    }
+                    double* L = sh_log.e + sh_cur.n * SHAPE_LOG_W;           // sh_cur.n < SHAPE_LOG_CAP: a full log is flushed below
+                    L[0] = t;
+                    L[1] = t_new;
+                    L[2] = (double)y[2];
+                    L[3] = Q[0];
+                    L[4] = Q[1];
+                    L[5] = Q[2];
+                    L[6] = Q[3];
+                    L[7] = __ddiv_rn(1.0, h_d);                                  // one division per accepted step
+                    sh_cur.n += 1;
                     info.shape_secs = sh_sec + 1;
                 }
 #pragma unroll
@@ -741,7 +806,11 @@ __device__ __forceinline__ void fk_dp45(const LaneId& id, bool valid, const Grou
             }
         }
         first = false;
+        if (SHAPE) {
+            if (__any_sync(FULL, sh_cur.n == SHAPE_LOG_CAP)) shape_flush<SHAPE>(gs, nsec, shape, sh_log, sh_cur);
+        }
     }
+    if (SHAPE) shape_flush<SHAPE>(gs, nsec, shape, sh_log, sh_cur);
     // zero-length spans cost one RHS call each and no step (base.py); a started section costs 2 calls (select_initial_step),
     // an attempt 6
     const int skipped = packed >> 8;
