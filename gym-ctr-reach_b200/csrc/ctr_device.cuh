@@ -398,6 +398,10 @@ __device__ __forceinline__ void build_sections(const double* L, const double* Lc
 // count is the largest number of samples + steps of a LANE, not the sum over the passes of the largest per-step count.
 constexpr int SHAPE_LOG_CAP = 24;
 constexpr int SHAPE_LOG_W = 8;
+#ifndef CTR_SHAPE_EMIT
+#define CTR_SHAPE_EMIT 2
+#endif
+constexpr int SHAPE_EMIT = CTR_SHAPE_EMIT;
 struct ShapeCursor {
     int sec, i;        // next sample to evaluate: abscissa i of section sec
     int n;             // steps in the log
@@ -425,22 +429,28 @@ __device__ __forceinline__ void shape_flush(const GroupScratch& gs, int nsec, co
                 have_sec = true;
             }
             if (have_sec && te <= t_new) {                                       // ivp.py: searchsorted(t_eval, t, 'right')
-                const double x = __dmul_rn(__dsub_rn(te, t_old), inv_h);         // differs from numpy's (te - t) / h by <= 1 ulp
-                const double x2 = __dmul_rn(x, x), x3 = __dmul_rn(x2, x), x4 = __dmul_rn(x3, x);   // np.cumprod
-                double acc = __dmul_rn(q0, x);
-                acc = __dadd_rn(acc, __dmul_rn(q1, x2));
-                acc = __dadd_rn(acc, __dmul_rn(q2, x3));
-                acc = __dadd_rn(acc, __dmul_rn(q3, x4));
-                if (pt < shape.max_pts) *out = __dadd_rn(__dmul_rn(h_d, acc), y_old);
-                out += shape.stride;
-                pt += 1;
-                cur.i += 1;
-                if (cur.i == SHAPE_SAMPLES) {
-                    cur.i = 0;
-                    cur.sec += 1;
-                    have_sec = false;
-                } else {
-                    te = shape_abscissa(cur.i, a, step, b);
+                // up to SHAPE_EMIT samples of this step per trip: most trips are samples (148 against 13 steps per lane on average),
+                // so the loop control (vote, branches, cursor bookkeeping) is shared between them
+#pragma unroll
+                for (int rep = 0; rep < SHAPE_EMIT; ++rep) {
+                    if (rep > 0 && !(have_sec && te <= t_new)) break;
+                    const double x = __dmul_rn(__dsub_rn(te, t_old), inv_h);     // differs from numpy's (te - t) / h by <= 1 ulp
+                    const double x2 = __dmul_rn(x, x), x3 = __dmul_rn(x2, x), x4 = __dmul_rn(x3, x);   // np.cumprod
+                    double acc = __dmul_rn(q0, x);
+                    acc = __dadd_rn(acc, __dmul_rn(q1, x2));
+                    acc = __dadd_rn(acc, __dmul_rn(q2, x3));
+                    acc = __dadd_rn(acc, __dmul_rn(q3, x4));
+                    if (pt < shape.max_pts) *out = __dadd_rn(__dmul_rn(h_d, acc), y_old);
+                    out += shape.stride;
+                    pt += 1;
+                    cur.i += 1;
+                    if (cur.i == SHAPE_SAMPLES) {
+                        cur.i = 0;
+                        cur.sec += 1;
+                        have_sec = false;
+                    } else {
+                        te = shape_abscissa(cur.i, a, step, b);
+                    }
                 }
             } else {                                                             // next step of the log
                 s += 1;
