@@ -182,3 +182,29 @@ def test_bvp_pass_is_independent_of_batch_shape_and_isolates_failed_rows(bvp, ve
     assert np.all(steps[bad] == -1) and np.all(np.isnan(tip[bad]))
     assert np.array_equal(steps[~bad], full['steps'][:64][~bad]) and np.array_equal(tip[~bad], full['tip'][:64][~bad])
     assert env.fault_counters()['fk_failed'] - before == 2
+
+
+@pytest.mark.gpu
+def test_bvp_argument_errors_and_joint_box_ends(oracle_c, oracle_py, vec_factory):
+    from ctr_reach_envs import _lib
+    env = vec_factory(8)
+    q = np.zeros((4, 6))
+    for bad in (0.0, -0.01, float('nan')):
+        with pytest.raises(_lib.CtrError):
+            env.bvp_pass(q, max_step=bad)
+        with pytest.raises(_lib.CtrError):
+            env.bvp_jacobian(q, max_step=bad)
+    rc = env.lib.ctr_bvp_pass(env.handle, None, None, None, None, None, 4, 0.01, None, None, None, None, env._stream())
+    assert rc != 0 and b'null' in env.lib.ctr_last_error()
+    # both ends of the joint box (fully extended, fully retracted) integrate without faults
+    import ctr_oracle as O
+    L = O.DEFAULT_SYSTEMS[0][:, 0]
+    ends = np.zeros((2, 6))
+    ends[1, :3] = -(L - 1e-3)
+    res = env.bvp_pass(ends)
+    assert (res['steps'].cpu().numpy() > 0).all() and np.isfinite(res['tip'].cpu().numpy()).all()
+    tcs = _tcs(oracle_c, oracle_py)
+    for i in range(2):                      # retracted: ~1 mm of straight tube along z (0.98 mm after Segment.py:16's 1e-5 quantisation)
+        o = oracle_c.bvp_pass(tcs[0], ends[i])
+        assert o['steps'] == int(res['steps'][i]) and np.abs(o['tip'] - res['tip'][i].cpu().numpy()).max() < 1e-12
+    assert abs(res['tip'].cpu().numpy()[1, 2] - 1e-3) < 5e-5
