@@ -131,6 +131,7 @@ struct KArgs {
     int64_t env_begin, env_count;               // env range of this launch (chunked host pipeline), whole handle by default
     int32_t* perm;             // slot -> env, sorted by last step's work inside windows of SORT_WINDOW slots (null: identity)
     int32_t* win_count;        // per-window arrival counters of the blocks (self-resetting)
+    int32_t interleave;        // block b serves rank b / W of window b % W (W windows in the launch) instead of rank b % 16 of window b / 16
 };
 
 __device__ __forceinline__ void stage_sys(SysConst* s_sys, const SysConst* sys, int n_systems) {
@@ -385,8 +386,20 @@ __global__ void CTR_FK_BOUNDS k_step(const KArgs a, const float* __restrict__ ac
     }
     unsigned pending = 0;          // group-leader lanes whose finished env must be reset in place
     int env32 = 0;                 // env index served by this lane's group
+    // Dispatch order: inside a sorting window the slots run from the heaviest env to the lightest.  With `interleave` the grid
+    // walks the windows round-robin -- the first W blocks are the heaviest block of every window, the last W the lightest of
+    // every window -- so the launch as a whole runs longest-first and drains on its shortest blocks (window by window the
+    // last ~600 resident blocks are a random mix of heavy and light ones).
+    int64_t lblk = (int64_t)blockIdx.x - a.refill_blocks;          // logical block: 40 consecutive slots
+    if (a.interleave && lblk >= 0) {
+        constexpr int BPW = SORT_WINDOW / ENVS_PER_BLOCK;
+        const int64_t nblk = (a.env_count + ENVS_PER_BLOCK - 1) / ENVS_PER_BLOCK;
+        const int64_t W = (nblk + BPW - 1) / BPW;
+        lblk = (lblk % W) * BPW + lblk / W;
+        if (lblk >= nblk) return;                                   // the last window has fewer blocks (block-uniform exit)
+    }
     if ((int)blockIdx.x >= a.refill_blocks) {
-        const int64_t warp = ((int64_t)(blockIdx.x - a.refill_blocks) * blockDim.x + threadIdx.x) >> 5;
+        const int64_t warp = (lblk * blockDim.x + threadIdx.x) >> 5;
         const int64_t local = warp * ENVS_PER_WARP + id.g;
         const bool valid = (id.g < ENVS_PER_WARP) && (local < a.env_count);
         // Work-sorted assignment: slot -> env through `perm`, which the previous step sorted by each env's RHS count
@@ -532,7 +545,7 @@ __global__ void CTR_FK_BOUNDS k_step(const KArgs a, const float* __restrict__ ac
         if (a.perm) {
             __shared__ int s_hist[256];
             __shared__ int s_last;
-            const int64_t blk = (int64_t)(blockIdx.x - a.refill_blocks);
+            const int64_t blk = lblk;
             constexpr int BLOCKS_PER_WINDOW = SORT_WINDOW / ENVS_PER_BLOCK;
             const int64_t win_local = blk / BLOCKS_PER_WINDOW;
             const int64_t slot0 = win_local * SORT_WINDOW;                           // first slot of the window, launch-relative
@@ -996,6 +1009,7 @@ struct ctr_handle {
     int32_t rq_cap;
     int64_t launches;
     int sm_count;
+    int block_interleave;      // k_step grid walks the sorting windows round-robin ($CTR_BLOCK_INTERLEAVE, default 1)
     int refill_blocks;         // leading blocks of a k_step launch that only drain the refill queue ($CTR_REFILL_BLOCKS, default sm_count / 2)
     // lazily allocated staging for host calls
     float* stage_action;
@@ -1100,6 +1114,7 @@ KArgs make_args(const ctr_handle* h) {
     a.env_begin = 0;
     a.env_count = h->n;
     a.perm = h->perm;
+    a.interleave = (h->perm && h->block_interleave) ? 1 : 0;
     a.win_count = h->win_count;
     return a;
 }
@@ -1229,6 +1244,7 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     cudaDeviceProp prop;
     CTR_CUDA(cudaGetDeviceProperties(&prop, device));
     h->sm_count = prop.multiProcessorCount;
+    h->block_interleave = getenv("CTR_BLOCK_INTERLEAVE") ? atoi(getenv("CTR_BLOCK_INTERLEAVE")) : 1;
     h->refill_blocks = getenv("CTR_REFILL_BLOCKS") ? atoi(getenv("CTR_REFILL_BLOCKS")) : h->sm_count / 2;   // sweep: profiles/r2i_refill_blocks_sweep.txt
     if (h->refill_blocks < 0) h->refill_blocks = 0;
     h->sys_host.resize(CTR_MAX_SYSTEMS);
@@ -1538,8 +1554,12 @@ static int launch_step_range(ctr_handle* h, KArgs a, const float* action_dev, in
     // U_y == 0 fast path: nominal tubes only (explicit per-env constants may carry any U_y)
     const bool uy0 = h->all_uy_zero && !h->use_params;
 #ifndef CTR_DEBUG_SKIP_STEP_KERNEL      // measurement-only build: the host pipeline's copies without its kernels
-    DISPATCH_STEP(uy0, h->cfg.integrator, h->cfg.precision,
-                  <<<grid_for(count) + refill_blocks, BLOCK, 0, st>>>(a, action_dev));
+    int grid = grid_for(count);
+    if (a.interleave) {                          // whole windows: the blocks past the last window's end leave at once
+        constexpr int BPW = SORT_WINDOW / ENVS_PER_BLOCK;
+        grid = ((grid + BPW - 1) / BPW) * BPW;
+    }
+    DISPATCH_STEP(uy0, h->cfg.integrator, h->cfg.precision, <<<grid + refill_blocks, BLOCK, 0, st>>>(a, action_dev));
 #else
     (void)uy0;
 #endif
