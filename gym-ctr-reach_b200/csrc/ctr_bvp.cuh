@@ -475,7 +475,7 @@ struct BvpLaneState {
     BvpLaneSec c;
     BvpLaneTube T;
     double fj, dtip, best, uz_tip, t, tf, h_abs;
-    int64_t p;                 // the pass (variant * n + configuration) being integrated
+    int64_t p;                 // output column (variant * n + configuration) of the pass being integrated
     int ksec, nsec, steps;
     bool done, have, exhausted, need_sec, rejected, failed;
 };
@@ -484,8 +484,11 @@ struct BvpLaneState {
 // only (no exchange inside; the caller synchronises the warp before the section table is read).
 template <bool LOAD>
 __device__ __forceinline__ void bvp_fetch(const BvpArgs& a, int j, int64_t p, GroupScratch& gs, BvpLaneState& s) {
-    const int v = (int)(p / a.n);
-    const int64_t i = p - (int64_t)v * a.n;
+    // scheduling order: the variants of one configuration are consecutive, so they run in the same warp at the same time -- they
+    // take (nearly) the same steps and start their sections together; the outputs keep the [rows][variant * n + i] layout
+    const int V = bvp_variants(a.mode);
+    const int64_t i = p / V;
+    const int v = (int)(p - i * V);
     double L[3], Lc[3], q[6], f[3] = {0.0, 0.0, 0.0}, u[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
     if (a.params) {
 #pragma unroll
@@ -573,7 +576,7 @@ __device__ __forceinline__ void bvp_fetch(const BvpArgs& a, int j, int64_t p, Gr
     s.ksec = 0;
     s.steps = 0;
     s.t = s.tf = s.h_abs = 0.0;
-    s.p = p;
+    s.p = (int64_t)v * a.n + i;                                 // where the results go
     s.done = false;
     s.have = true;
     s.need_sec = true;
