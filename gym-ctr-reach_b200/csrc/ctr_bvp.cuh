@@ -301,6 +301,7 @@ struct BvpArgs {
     int32_t* steps;         // i32 [V n] or null
     double* fault;          // stats slot for failed passes or null
     unsigned long long* next;  // work counter of the persistent lane-group kernel (zeroed before the launch)
+    const int32_t* order;      // configuration served by scheduling rank r (k_bvp_order_*), or null: rank r is configuration r
 };
 
 __device__ __host__ inline int bvp_variants(int mode) { return 1 + ((mode & 1) ? 6 : 0) + ((mode & 2) ? 3 : 0) + ((mode & 4) ? 5 : 0); }
@@ -359,7 +360,9 @@ __global__ void __launch_bounds__(CTR_BVP_BLOCK, CTR_BVP_MINB) k_bvp_pass(const 
     }
     if (w >= 0 && (a.mode & 4) && w < 5) u[w] = __dadd_rn(u[w], a.eps_u);
     double y[NB], cost[5];
-    const int st = bvp_pass(C, q, f, u, a.max_step, a.rtol, a.atol, y, cost);
+    bool finite = true;
+    for (int k = 0; k < 6; ++k) finite = finite && fabs(q[k]) < CUDART_INF;
+    const int st = finite ? bvp_pass(C, q, f, u, a.max_step, a.rtol, a.atol, y, cost) : -1;
     const int64_t M = (int64_t)V * a.n;
     const double bad = __longlong_as_double(0x7ff8000000000000LL);
     for (int k = 0; k < 3; ++k) a.tip[(int64_t)k * M + p] = (st < 0) ? bad : y[8 + k];
@@ -487,8 +490,9 @@ __device__ __forceinline__ void bvp_fetch(const BvpArgs& a, int j, int64_t p, Gr
     // scheduling order: the variants of one configuration are consecutive, so they run in the same warp at the same time -- they
     // take (nearly) the same steps and start their sections together; the outputs keep the [rows][variant * n + i] layout
     const int V = bvp_variants(a.mode);
-    const int64_t i = p / V;
-    const int v = (int)(p - i * V);
+    const int64_t r = p / V;
+    const int v = (int)(p - r * V);
+    const int64_t i = a.order ? (int64_t)a.order[r] : r;
     double L[3], Lc[3], q[6], f[3] = {0.0, 0.0, 0.0}, u[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
     if (a.params) {
 #pragma unroll
@@ -577,11 +581,14 @@ __device__ __forceinline__ void bvp_fetch(const BvpArgs& a, int j, int64_t p, Gr
     s.steps = 0;
     s.t = s.tf = s.h_abs = 0.0;
     s.p = (int64_t)v * a.n + i;                                 // where the results go
-    s.done = false;
+    // a NaN / infinite joint has no section table (every comparison of Segment.py is false): a failed pass, not an empty one
+    const bool finite = fabs(q[0]) < CUDART_INF && fabs(q[1]) < CUDART_INF && fabs(q[2]) < CUDART_INF && fabs(q[3]) < CUDART_INF &&
+                        fabs(q[4]) < CUDART_INF && fabs(q[5]) < CUDART_INF;
+    s.done = !finite;
     s.have = true;
     s.need_sec = true;
     s.rejected = false;
-    s.failed = false;
+    s.failed = !finite;
 }
 
 // residuals (:228-235) and the tip frame of a finished pass: lane 0 owns cost 0..2, lanes 1 / 2 the twist of their tube at its tip
@@ -656,7 +663,10 @@ __global__ void __launch_bounds__(CTR_BLOCK, CTR_BVP_GMINB) k_bvp_pass_g(const B
             __syncwarp();
             if (want && !s.exhausted) s.nsec = gs.nsec & 0xff;
         }
-        if (!__any_sync(FULL, !s.done)) break;
+        if (!__any_sync(FULL, !s.done)) {
+            if (__any_sync(FULL, s.have)) continue;              // passes that failed at fetch are stored at the top of the loop
+            break;
+        }
         bool init = false;
         if (__any_sync(FULL, s.need_sec && !s.done)) {
             // ---- next section: moment continuity gives u_1xy of the new section (:186-226), executed by the whole warp
@@ -791,6 +801,68 @@ __global__ void __launch_bounds__(CTR_BLOCK, CTR_BVP_GMINB) k_bvp_pass_g(const B
             }
         }
     }
+}
+
+// ---- scheduling order of the configurations --------------------------------------------------------------------------------
+// The groups of a warp run their passes independently, but a warp whose 10 passes look alike wastes less: its sections start in the
+// same iterations (the initial-step block runs for several groups at once) and its groups run dry together.  Passes that are
+// handed out in an order that puts similar configurations next to each other, the long ones first, finish sooner: measured on
+// 131072 reset configurations 2.17 ms in the given order, 1.59 ms sorted by the (unknowable) step count itself, 1.74 ms by the key
+// used here -- few sections first (passes with few, long sections take the most steps), longer robots first among those.  Any order
+// gives the same results (outputs are addressed by configuration).  Counting sort: key + histogram, scan of the 256 bins, scatter.
+__global__ void k_bvp_order_key(const BvpArgs a, uint8_t* __restrict__ key, int32_t* __restrict__ hist) {
+    __shared__ int s_hist[256];
+    for (int k = threadIdx.x; k < 256; k += blockDim.x) s_hist[k] = 0;
+    __syncthreads();
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < a.n) {
+        double L[3], Lc[3], beta[3];
+        if (a.params) {
+            for (int k = 0; k < 3; ++k) {
+                L[k] = a.params[(int64_t)k * a.n + i];
+                Lc[k] = a.params[(int64_t)(3 + k) * a.n + i];
+            }
+        } else {
+            int sy = a.system ? a.system[i] : 0;
+            sy = min(max(sy, 0), a.n_systems - 1);
+            for (int k = 0; k < 3; ++k) {
+                L[k] = a.sys[sy].L[k];
+                Lc[k] = a.sys[sy].Lc[k];
+            }
+        }
+        for (int k = 0; k < 3; ++k) beta[k] = a.q[(int64_t)k * a.n + i];
+        double S[9];
+        int pat[9];
+        int m = bvp_sections(L, Lc, beta, S, pat);
+        const double len = m > 0 ? S[m - 1] : 0.0, lmax = fmax(fmax(L[0], L[1]), L[2]);
+        int lb = 15 - (int)(16.0 * len / lmax);                         // longer first
+        lb = min(max(lb, 0), 15);
+        m = min(max(m, 0), 15);
+        const int kk = (len == len) ? m * 16 + lb : 255;                // NaN joints last
+        key[i] = (uint8_t)kk;
+        atomicAdd(&s_hist[kk], 1);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < 256; k += blockDim.x)
+        if (s_hist[k]) atomicAdd(&hist[k], s_hist[k]);
+}
+__global__ void k_bvp_order_scan(int32_t* __restrict__ hist) {          // one block of 256 threads: exclusive scan in place
+    __shared__ int s[256];
+    const int t = threadIdx.x;
+    s[t] = hist[t];
+    __syncthreads();
+    for (int o = 1; o < 256; o <<= 1) {
+        const int v = (t >= o) ? s[t - o] : 0;
+        __syncthreads();
+        s[t] += v;
+        __syncthreads();
+    }
+    hist[t] = s[t] - hist[t];
+}
+__global__ void k_bvp_order_scatter(int64_t n, const uint8_t* __restrict__ key, int32_t* __restrict__ offs, int32_t* __restrict__ order) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    order[atomicAdd(&offs[key[i]], 1)] = (int32_t)i;
 }
 
 // Forward differences over the variant block: J f64 [18][n] (3 x 6 row-major), Cm f64 [9][n] (3 x 3), tip0 f64 [3][n]

@@ -1029,6 +1029,9 @@ struct ctr_handle {
     void* bvp_dev;
     unsigned long long* bvp_next;   // work counters of k_bvp_pass_g (ring of 64)
     unsigned bvp_launches;
+    void* bvp_order_dev;       // scheduling order of k_bvp_pass_g: order i32 [cap] | hist i32 [256] | key u8 [cap]
+    int64_t bvp_order_cap;
+    int bvp_sort;              // order the configurations before a launch ($CTR_BVP_SORT, default 1; from 4096 configurations on)
     int64_t ik_cap;            // ctr_jacobian / ctr_ik_dls scratch: joints f64 [6][7n] | tips f64 [3][7n] | system i32 [7n] | frozen u8 [n] | active i32
     void* ik_dev;
 };
@@ -1240,6 +1243,9 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     h->bvp_dev = nullptr;
     h->bvp_next = nullptr;
     h->bvp_launches = 0;
+    h->bvp_order_dev = nullptr;
+    h->bvp_order_cap = 0;
+    h->bvp_sort = getenv("CTR_BVP_SORT") ? atoi(getenv("CTR_BVP_SORT")) : 1;
     jacobian_scratch_resolve(h->device, nullptr);   // ctr_jacobian_noalloc: device address of its static scratch, once per device (its error, if any, is reported by that call)
     cudaDeviceProp prop;
     CTR_CUDA(cudaGetDeviceProperties(&prop, device));
@@ -1371,6 +1377,7 @@ int ctr_destroy(ctr_handle* h) {
     if (h->ik_dev) cudaFree(h->ik_dev);
     if (h->bvp_dev) cudaFree(h->bvp_dev);
     if (h->bvp_next) cudaFree(h->bvp_next);
+    if (h->bvp_order_dev) cudaFree(h->bvp_order_dev);
     if (h->stream) cudaStreamDestroy(h->stream);
     for (int k = 1; k <= N_COMPUTE_STREAMS; ++k) {
         if (h->streams[k]) cudaStreamDestroy(h->streams[k]);
@@ -2389,6 +2396,24 @@ static int bvp_launch(ctr_handle* h, const BvpArgs& a_in, cudaStream_t st) {
         if (!h->bvp_next) CTR_CUDA(cudaMalloc(&h->bvp_next, 64 * sizeof(unsigned long long)));
         a.next = h->bvp_next + (h->bvp_launches++ & 63);
         CTR_CUDA(cudaMemsetAsync(a.next, 0, sizeof(unsigned long long), st));
+        if (h->bvp_sort && a.n >= 4096 && a.n < (int64_t)1 << 31) {     // scheduling order (k_bvp_order_*): similar configurations together, long ones first
+            if (h->bvp_order_cap < a.n) {
+                if (h->bvp_order_dev) CTR_CUDA(cudaFree(h->bvp_order_dev));
+                h->bvp_order_dev = nullptr;
+                h->bvp_order_cap = 0;
+                CTR_CUDA(cudaMalloc(&h->bvp_order_dev, (size_t)a.n * 5 + 1024 + 64));
+                h->bvp_order_cap = a.n;
+            }
+            int32_t* order = (int32_t*)h->bvp_order_dev;
+            int32_t* hist = order + h->bvp_order_cap;
+            uint8_t* key = (uint8_t*)(hist + 256);
+            CTR_CUDA(cudaMemsetAsync(hist, 0, 256 * sizeof(int32_t), st));
+            k_bvp_order_key<<<(int)((a.n + 255) / 256), 256, 0, st>>>(a, key, hist);
+            k_bvp_order_scan<<<1, 256, 0, st>>>(hist);
+            k_bvp_order_scatter<<<(int)((a.n + 255) / 256), 256, 0, st>>>(a.n, key, hist, order);
+            h->launches += 3;
+            a.order = order;
+        }
         const int per_block = (CTR_BLOCK / 32) * 10;     // 3 lanes per pass, 10 passes in flight per warp
         int64_t grid = (total + per_block - 1) / per_block;
         const int64_t resident = (int64_t)h->sm_count * CTR_BVP_GMINB;   // persistent: the groups refill themselves from a.next

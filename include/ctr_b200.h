@@ -291,8 +291,10 @@ int ctr_jacobian_noalloc(ctr_handle *h, const double *joints_dev, const int32_t 
  *                     res [n] final residual max-norm, iters i32 [n]; tip / cost of the pass at the solution optional.  Synchronises.
  * ctr_bvp_ik_dls    = src/jacobian_controller.py:19-53 on this model: q [6][n] in/out, target [3][n]; as ctr_ik_dls.  Synchronises.
  * Streams: ctr_bvp_jacobian / _solve / _ik_dls keep their intermediate results in ONE scratch buffer of the handle (grown with
- * cudaMalloc on demand): calls on the same handle must not overlap on the GPU (one stream, or one handle per stream).  ctr_bvp_pass
- * has no such buffer; its pass-scheduling counter comes from a ring of 64, so up to 64 of its launches may be in flight at once. */
+ * cudaMalloc on demand): calls on the same handle must not overlap on the GPU (one stream, or one handle per stream).  The same
+ * holds for ctr_bvp_pass from 4096 configurations on (its scheduling order -- which configuration a free lane group takes next; it
+ * does not change any result -- is built in a buffer of the handle); below that it keeps no state but a pass counter taken from a
+ * ring of 64, so up to 64 such launches may be in flight at once. */
 int ctr_bvp_pass(ctr_handle *h, const double *q_dev, const double *f_dev, const double *u_dev, const int32_t *system_dev,
                  const double *params_dev, int64_t n, double max_step, double *tip_dev, double *R_dev, double *cost_dev,
                  int32_t *steps_dev, void *stream);
