@@ -2226,17 +2226,14 @@ static int ik_scratch(ctr_handle* h, int64_t n, IkScratch* out) {
 // the 7n kinematics solves of one Jacobian: unperturbed + one column block per joint
 static int ik_solve7(ctr_handle* h, const IkScratch& sc, const double* q_dev, const int32_t* system_dev, int64_t n, double eps,
                      cudaStream_t st) {
-    k_ik_perturb<<<(int)((n + 255) / 256), 256, 0, st>>>(q_dev, n, eps, sc.block);
+    k_ik_perturb<<<(int)((n + 255) / 256), 256, 0, st>>>(q_dev, system_dev, n, eps, sc.block, system_dev ? sc.system : nullptr);
     h->launches += 1;
     CTR_CUDA(cudaGetLastError());
     return ctr_fk(h, sc.block, system_dev ? sc.system : nullptr, nullptr, 7 * n, CTR_INTEGRATOR_DP45, CTR_PRECISION_F64, sc.tips,
                   nullptr, nullptr, st);
 }
-static int ik_systems(const IkScratch& sc, const int32_t* system_dev, int64_t n, cudaStream_t st) {
-    if (!system_dev) return 0;
-    for (int k = 0; k < 7; ++k)
-        CTR_CUDA(cudaMemcpyAsync(sc.system + (int64_t)k * n, system_dev, sizeof(int32_t) * n, cudaMemcpyDeviceToDevice, st));
-    return 0;
+static int ik_systems(const IkScratch&, const int32_t*, int64_t, cudaStream_t) {
+    return 0;                                    // the system ids of the 7n columns are written by k_ik_perturb (same layout as the joints)
 }
 
 int ctr_jacobian(ctr_handle* h, const double* joints_dev, const int32_t* system_dev, int64_t n, double eps, double* J_dev,
@@ -2262,7 +2259,7 @@ int ctr_jacobian(ctr_handle* h, const double* joints_dev, const int32_t* system_
 // tips and the 7n system ids live in ONE file-scope device array instead of the handle's grow-on-demand allocation.  Every
 // GPU that loads the library holds the array (CTR_JACOBIAN_NOALLOC_MAX * 532 B = 8.3 MiB) until the process exits.  Every
 // call on a device shares it: calls that overlap on the GPU (different streams, different handles of one device) race.
-// Nothing in it has to start at zero -- k_ik_perturb writes all 42n joint values, the system copies all 7n ids and k_fk all 21n
+// Nothing in it has to start at zero -- k_ik_perturb writes all 42n joint values, it also writes all 7n system ids, and k_fk all 21n
 // tip values (NaN for a failed solve) before k_ik_jacobian reads them -- so the previous call's contents are never seen.
 constexpr int64_t NOALLOC_BYTES_PER_CONFIG = 7 * 6 * 8 + 7 * 3 * 8 + 7 * 4;
 static __device__ __align__(256) unsigned char g_jacobian_scratch[CTR_JACOBIAN_NOALLOC_MAX * NOALLOC_BYTES_PER_CONFIG];
