@@ -810,7 +810,8 @@ __global__ void __launch_bounds__(CTR_BLOCK, CTR_BVP_GMINB) k_bvp_pass_g(const B
 // 131072 reset configurations 2.17 ms in the given order, 1.59 ms sorted by the (unknowable) step count itself, 1.74 ms by the key
 // used here -- few sections first (passes with few, long sections take the most steps), longer robots first among those.  Any order
 // gives the same results (outputs are addressed by configuration).  Counting sort: key + histogram, scan of the 256 bins, scatter.
-__global__ void k_bvp_order_key(const BvpArgs a, uint8_t* __restrict__ key, int32_t* __restrict__ hist) {
+// many_first: the env path's solves (k_fk) cost a fixed price per section, so there the configurations with MANY sections are the long ones
+__global__ void k_bvp_order_key(const BvpArgs a, int many_first, uint8_t* __restrict__ key, int32_t* __restrict__ hist) {
     __shared__ int s_hist[256];
     for (int k = threadIdx.x; k < 256; k += blockDim.x) s_hist[k] = 0;
     __syncthreads();
@@ -838,6 +839,7 @@ __global__ void k_bvp_order_key(const BvpArgs a, uint8_t* __restrict__ key, int3
         int lb = 15 - (int)(16.0 * len / lmax);                         // longer first
         lb = min(max(lb, 0), 15);
         m = min(max(m, 0), 15);
+        if (many_first) m = 15 - m;
         const int kk = (len == len) ? m * 16 + lb : 255;                // NaN joints last
         key[i] = (uint8_t)kk;
         atomicAdd(&s_hist[kk], 1);

@@ -37,15 +37,18 @@ __global__ void k_ik_perturb(const double* __restrict__ q, const int32_t* __rest
 }
 
 // tips f64 [3][7n] -> J f64 [18][n], row-major 3 x 6: J[r][c] = (tip_c+1[r] - tip_0[r]) / eps   (CTR_Model.py:259-260)
+// CM (configuration major): solve k of configuration i is column 7 i + k (k_ik_perturb); otherwise k n + i (the variant blocks of
+// the BVP back-end's launches, csrc/ctr_bvp.cuh)
+template <bool CM>
 __device__ __forceinline__ void fd_jacobian(const double* __restrict__ tips, int64_t n, int64_t i, double eps, double (&P)[3],
                                             double (&J)[3][6]) {
 #pragma unroll
-    for (int r = 0; r < 3; ++r) P[r] = tips[(int64_t)r * 7 * n + 7 * i];
+    for (int r = 0; r < 3; ++r) P[r] = tips[(int64_t)r * 7 * n + (CM ? 7 * i : i)];
 #pragma unroll
     for (int c = 0; c < 6; ++c)
 #pragma unroll
         for (int r = 0; r < 3; ++r)
-            J[r][c] = __ddiv_rn(__dsub_rn(tips[(int64_t)r * 7 * n + 7 * i + (c + 1)], P[r]), eps);
+            J[r][c] = __ddiv_rn(__dsub_rn(tips[(int64_t)r * 7 * n + (CM ? 7 * i + (c + 1) : (int64_t)(c + 1) * n + i)], P[r]), eps);
 }
 
 __global__ void k_ik_jacobian(const double* __restrict__ tips, int64_t n, double eps, double* __restrict__ Jout,
@@ -53,7 +56,7 @@ __global__ void k_ik_jacobian(const double* __restrict__ tips, int64_t n, double
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     double P[3], J[3][6];
-    fd_jacobian(tips, n, i, eps, P, J);
+    fd_jacobian<true>(tips, n, i, eps, P, J);
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
         if (tip0) tip0[(int64_t)r * n + i] = P[r];
@@ -65,13 +68,14 @@ __global__ void k_ik_jacobian(const double* __restrict__ tips, int64_t n, double
 // One DLS iteration for every configuration that has not converged (jacobian_controller.py:41-53):
 //   e = target - P;  q += J^T (J J^T + lam I)^-1 e;  converged once ||e|| < tol (the update of that iteration is applied).
 // err[i] = ||e|| of the last iteration run, iters[i] = iterations run, active[0] counts the configurations still iterating.
+template <bool CM>
 __global__ void k_ik_dls_update(const double* __restrict__ tips, const double* __restrict__ target, int64_t n, double eps,
                                 double lam, double tol, double* __restrict__ q, double* __restrict__ err,
                                 int32_t* __restrict__ iters, uint8_t* __restrict__ frozen, int32_t* __restrict__ active) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n || frozen[i]) return;
     double P[3], J[3][6], e[3];
-    fd_jacobian(tips, n, i, eps, P, J);
+    fd_jacobian<CM>(tips, n, i, eps, P, J);
 #pragma unroll
     for (int r = 0; r < 3; ++r) e[r] = __dsub_rn(target[(int64_t)r * n + i], P[r]);
     double A[3][3];                                                   // J J^T + lam I (symmetric)

@@ -220,14 +220,17 @@ __global__ void CTR_FK_BOUNDS k_fk(const SysConst* __restrict__ sys, int n_syste
                                               const double* __restrict__ joints, const int32_t* __restrict__ system,
                                               const double* __restrict__ params, int64_t n, double rtol, double atol,
                                               int rk4_steps, double* __restrict__ tip, double* __restrict__ R,
-                                              int32_t* __restrict__ info_out, double* __restrict__ stats) {
+                                              int32_t* __restrict__ info_out, double* __restrict__ stats,
+                                              const int32_t* __restrict__ order, int group) {
     __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
     __shared__ GroupScratch s_gs[(BLOCK / 32) * SLOTS_PER_WARP];
     stage_sys(s_sys, sys, n_systems);
     const LaneId id = lane_id();
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t env = warp * ENVS_PER_WARP + id.g;
-    const bool valid = (id.g < ENVS_PER_WARP) && (env < n);
+    const int64_t slot = warp * ENVS_PER_WARP + id.g;
+    const bool valid = (id.g < ENVS_PER_WARP) && (slot < n);
+    // work-sorted hand-out order (fk_order): slot -> column; `group` consecutive columns (the 7 solves of a Jacobian) stay together
+    const int64_t env = (valid && order) ? (int64_t)order[slot / group] * group + slot % group : slot;
     const int64_t e = valid ? env : 0;
     int sysid = system ? system[e] : 0;
     sysid = min(max(sysid, 0), n_systems - 1);
@@ -269,14 +272,15 @@ __global__ void CTR_FK_BOUNDS k_fk_shape(const SysConst* __restrict__ sys, int n
                                                     const double* __restrict__ params, int64_t n, double rtol, double atol,
                                                     int max_pts, double* __restrict__ shape, int32_t* __restrict__ npts,
                                                     int32_t* __restrict__ tip_idx, double* __restrict__ tip,
-                                                    double* __restrict__ stats) {
+                                                    double* __restrict__ stats, const int32_t* __restrict__ order) {
     __shared__ SysConst s_sys[CTR_MAX_SYSTEMS];
     __shared__ GroupScratch s_gs[(BLOCK / 32) * SLOTS_PER_WARP];
     stage_sys(s_sys, sys, n_systems);
     const LaneId id = lane_id();
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t env = warp * ENVS_PER_WARP + id.g;
-    const bool valid = (id.g < ENVS_PER_WARP) && (env < n);
+    const int64_t slot = warp * ENVS_PER_WARP + id.g;
+    const bool valid = (id.g < ENVS_PER_WARP) && (slot < n);
+    const int64_t env = (valid && order) ? (int64_t)order[slot] : slot;
     const int64_t e = valid ? env : 0;
     int sysid = system ? system[e] : 0;
     sysid = min(max(sysid, 0), n_systems - 1);
@@ -1031,7 +1035,7 @@ struct ctr_handle {
     unsigned bvp_launches;
     void* bvp_order_dev;       // scheduling order of k_bvp_pass_g: order i32 [cap] | hist i32 [256] | key u8 [cap]
     int64_t bvp_order_cap;
-    int bvp_sort;              // order the configurations before a launch ($CTR_BVP_SORT, default 1; from 4096 configurations on)
+    int bvp_sort;              // order the configurations before a k_bvp_pass_g / k_fk / k_fk_shape launch ($CTR_BVP_SORT or $CTR_FK_SORT, default 1; from 4096 configurations on)
     int64_t ik_cap;            // ctr_jacobian / ctr_ik_dls scratch: joints f64 [6][7n] | tips f64 [3][7n] | system i32 [7n] | frozen u8 [n] | active i32
     void* ik_dev;
 };
@@ -1245,7 +1249,7 @@ int ctr_create(const ctr_config* cfg, int64_t n_envs, int32_t device, ctr_handle
     h->bvp_launches = 0;
     h->bvp_order_dev = nullptr;
     h->bvp_order_cap = 0;
-    h->bvp_sort = getenv("CTR_BVP_SORT") ? atoi(getenv("CTR_BVP_SORT")) : 1;
+    h->bvp_sort = getenv("CTR_BVP_SORT") ? atoi(getenv("CTR_BVP_SORT")) : (getenv("CTR_FK_SORT") ? atoi(getenv("CTR_FK_SORT")) : 1);
     jacobian_scratch_resolve(h->device, nullptr);   // ctr_jacobian_noalloc: device address of its static scratch, once per device (its error, if any, is reported by that call)
     cudaDeviceProp prop;
     CTR_CUDA(cudaGetDeviceProperties(&prop, device));
@@ -1458,21 +1462,37 @@ int ctr_set_tube_params(ctr_handle* h, const double* params_dev, void* stream) {
     return mark_user_work(h, (cudaStream_t)stream);
 }
 
+// Work-sorted hand-out order of n configurations (k_bvp_order_* in ctr_bvp.cuh: counting sort on section count and deployed length)
+// in the handle's order buffer; *order = null below 4096 configurations or with $CTR_FK_SORT=0 / $CTR_BVP_SORT=0.
+static int build_order(ctr_handle* h, const double* q_dev, const int32_t* system_dev, const double* params_dev, int64_t n,
+                       int many_first, cudaStream_t st, const int32_t** order_out);
+
+// columns = n_cols joint columns; order (or null) permutes groups of `group` consecutive columns
+static int fk_launch(ctr_handle* h, const double* joints_dev, const int32_t* system_dev, const double* params_dev, int64_t n,
+                     int32_t integrator, int32_t precision, double* tip_dev, double* R_dev, int32_t* info_dev, cudaStream_t st,
+                     const int32_t* order, int group) {
+    if (integrator < 0) integrator = h->cfg.integrator;
+    if (precision < 0) precision = h->cfg.precision;
+    int rk4 = h->cfg.rk4_steps > 0 ? h->cfg.rk4_steps : 8;
+    DISPATCH(k_fk, integrator, precision,
+             <<<grid_for(n), BLOCK, 0, st>>>(h->sys_dev, h->cfg.n_systems, joints_dev, system_dev, params_dev, n,
+                                             h->cfg.rtol, h->cfg.atol, rk4, tip_dev, R_dev, info_dev, h->p.stats, order, group));
+    h->launches += 1;
+    CTR_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int ctr_fk(ctr_handle* h, const double* joints_dev, const int32_t* system_dev, const double* params_dev, int64_t n,
            int32_t integrator, int32_t precision, double* tip_dev, double* R_dev, int32_t* info_dev, void* stream) {
     if (!h || !joints_dev || !tip_dev) CTR_FAIL("null argument");
     if (n <= 0) return 0;
     CTR_CUDA(cudaSetDevice(h->device));
-    if (integrator < 0) integrator = h->cfg.integrator;
-    if (precision < 0) precision = h->cfg.precision;
-    int rk4 = h->cfg.rk4_steps > 0 ? h->cfg.rk4_steps : 8;
     cudaStream_t st = (cudaStream_t)stream;
-    DISPATCH(k_fk, integrator, precision,
-             <<<grid_for(n), BLOCK, 0, st>>>(h->sys_dev, h->cfg.n_systems, joints_dev, system_dev, params_dev, n,
-                                             h->cfg.rtol, h->cfg.atol, rk4, tip_dev, R_dev, info_dev, h->p.stats));
-    h->launches += 1;
-    CTR_CUDA(cudaGetLastError());
-    return 0;
+    // a lock-step warp costs its longest solve: hand the configurations out sorted by what their section tables say about their length
+    const int32_t* order = nullptr;
+    int rc = build_order(h, joints_dev, system_dev, params_dev, n, 1, st, &order);
+    if (rc) return rc;
+    return fk_launch(h, joints_dev, system_dev, params_dev, n, integrator, precision, tip_dev, R_dev, info_dev, st, order, 1);
 }
 
 int ctr_fk_host(ctr_handle* h, const double* joints_host, const int32_t* system_host, int64_t n, int32_t integrator,
@@ -2186,14 +2206,19 @@ int ctr_fk_shape(ctr_handle* h, const double* joints_dev, const int32_t* system_
     if (max_pts < 1) CTR_FAIL("max_pts must be >= 1");
     if (n <= 0) return 0;
     CTR_CUDA(cudaSetDevice(h->device));
+    const int32_t* order = nullptr;              // work-sorted hand-out order, as for ctr_fk
+    {
+        int rc = build_order(h, joints_dev, system_dev, params_dev, n, 1, (cudaStream_t)stream, &order);
+        if (rc) return rc;
+    }
     if (h->all_uy_zero && !params_dev)
         k_fk_shape<true><<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(h->sys_dev, h->cfg.n_systems, joints_dev, system_dev, params_dev, n,
                                                                          h->cfg.rtol, h->cfg.atol, max_pts, shape_dev, npts_dev,
-                                                                         tip_idx_dev, tip_dev, h->p.stats);
+                                                                         tip_idx_dev, tip_dev, h->p.stats, order);
     else
         k_fk_shape<false><<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(h->sys_dev, h->cfg.n_systems, joints_dev, system_dev, params_dev, n,
                                                                           h->cfg.rtol, h->cfg.atol, max_pts, shape_dev, npts_dev,
-                                                                          tip_idx_dev, tip_dev, h->p.stats);
+                                                                          tip_idx_dev, tip_dev, h->p.stats, order);
     h->launches += 1;
     CTR_CUDA(cudaGetLastError());
     return 0;
@@ -2225,12 +2250,15 @@ static int ik_scratch(ctr_handle* h, int64_t n, IkScratch* out) {
 }
 // the 7n kinematics solves of one Jacobian: unperturbed + one column block per joint
 static int ik_solve7(ctr_handle* h, const IkScratch& sc, const double* q_dev, const int32_t* system_dev, int64_t n, double eps,
-                     cudaStream_t st) {
+                     cudaStream_t st, bool sorted = true) {
     k_ik_perturb<<<(int)((n + 255) / 256), 256, 0, st>>>(q_dev, system_dev, n, eps, sc.block, system_dev ? sc.system : nullptr);
     h->launches += 1;
     CTR_CUDA(cudaGetLastError());
-    return ctr_fk(h, sc.block, system_dev ? sc.system : nullptr, nullptr, 7 * n, CTR_INTEGRATOR_DP45, CTR_PRECISION_F64, sc.tips,
-                  nullptr, nullptr, st);
+    const int32_t* order = nullptr;              // configurations in work-sorted order, the 7 columns of each one together
+    int rc = sorted ? build_order(h, q_dev, system_dev, nullptr, n, 1, st, &order) : 0;   // (the order buffer is a cudaMalloc: not for ctr_jacobian_noalloc)
+    if (rc) return rc;
+    return fk_launch(h, sc.block, system_dev ? sc.system : nullptr, nullptr, 7 * n, CTR_INTEGRATOR_DP45, CTR_PRECISION_F64, sc.tips,
+                     nullptr, nullptr, st, order, 7);
 }
 static int ik_systems(const IkScratch&, const int32_t*, int64_t, cudaStream_t) {
     return 0;                                    // the system ids of the 7n columns are written by k_ik_perturb (same layout as the joints)
@@ -2306,7 +2334,7 @@ int ctr_jacobian_noalloc(ctr_handle* h, const double* joints_dev, const int32_t*
     sc.active = nullptr;
     sc.frozen = nullptr;
     int rc = ik_systems(sc, system_dev, n, st);
-    if (!rc) rc = ik_solve7(h, sc, joints_dev, system_dev, n, eps, st);
+    if (!rc) rc = ik_solve7(h, sc, joints_dev, system_dev, n, eps, st, false);   // given order: no order buffer, no allocation
     if (rc) return rc;
     k_ik_jacobian<<<(int)((n + 255) / 256), 256, 0, st>>>(sc.tips, n, eps, J_dev, tip_dev);
     h->launches += 1;
@@ -2332,7 +2360,7 @@ int ctr_ik_dls(ctr_handle* h, const double* target_dev, double* joints_dev, cons
         CTR_CUDA(cudaMemsetAsync(sc.active, 0, sizeof(int32_t), st));
         rc = ik_solve7(h, sc, joints_dev, system_dev, n, eps, st);
         if (rc) return rc;
-        k_ik_dls_update<<<(int)((n + 255) / 256), 256, 0, st>>>(sc.tips, target_dev, n, eps, lam, tol, joints_dev, err_dev, iters_dev,
+        k_ik_dls_update<true><<<(int)((n + 255) / 256), 256, 0, st>>>(sc.tips, target_dev, n, eps, lam, tol, joints_dev, err_dev, iters_dev,
                                                                sc.frozen, sc.active);
         h->launches += 1;
         CTR_CUDA(cudaGetLastError());
@@ -2382,6 +2410,38 @@ static BvpArgs bvp_args(ctr_handle* h, const double* q, const double* f, const d
     a.fault = h->p.stats + ST_FK_FAILED;
     return a;
 }
+static int build_order(ctr_handle* h, const double* q_dev, const int32_t* system_dev, const double* params_dev, int64_t n,
+                       int many_first, cudaStream_t st, const int32_t** order_out) {
+    *order_out = nullptr;
+    if (!h->bvp_sort || n < 4096 || n >= (int64_t)1 << 31) return 0;
+    if (h->bvp_order_cap < n) {
+        if (h->bvp_order_dev) CTR_CUDA(cudaFree(h->bvp_order_dev));
+        h->bvp_order_dev = nullptr;
+        h->bvp_order_cap = 0;
+        CTR_CUDA(cudaMalloc(&h->bvp_order_dev, (size_t)n * 5 + 1024 + 64));
+        h->bvp_order_cap = n;
+    }
+    int32_t* order = (int32_t*)h->bvp_order_dev;
+    int32_t* hist = order + h->bvp_order_cap;
+    uint8_t* key = (uint8_t*)(hist + 256);
+    BvpArgs a;
+    memset(&a, 0, sizeof a);
+    a.sys = h->sys_dev;
+    a.n_systems = h->cfg.n_systems;
+    a.q = q_dev;
+    a.system = system_dev;
+    a.params = params_dev;
+    a.n = n;
+    CTR_CUDA(cudaMemsetAsync(hist, 0, 256 * sizeof(int32_t), st));
+    k_bvp_order_key<<<(int)((n + 255) / 256), 256, 0, st>>>(a, many_first, key, hist);
+    k_bvp_order_scan<<<1, 256, 0, st>>>(hist);
+    k_bvp_order_scatter<<<(int)((n + 255) / 256), 256, 0, st>>>(n, key, hist, order);
+    h->launches += 3;
+    CTR_CUDA(cudaGetLastError());
+    *order_out = order;
+    return 0;
+}
+
 static int bvp_launch(ctr_handle* h, const BvpArgs& a_in, cudaStream_t st) {
     BvpArgs a = a_in;
     const int64_t total = (int64_t)bvp_variants(a.mode) * a.n;
@@ -2393,22 +2453,10 @@ static int bvp_launch(ctr_handle* h, const BvpArgs& a_in, cudaStream_t st) {
         if (!h->bvp_next) CTR_CUDA(cudaMalloc(&h->bvp_next, 64 * sizeof(unsigned long long)));
         a.next = h->bvp_next + (h->bvp_launches++ & 63);
         CTR_CUDA(cudaMemsetAsync(a.next, 0, sizeof(unsigned long long), st));
-        if (h->bvp_sort && a.n >= 4096 && a.n < (int64_t)1 << 31) {     // scheduling order (k_bvp_order_*): similar configurations together, long ones first
-            if (h->bvp_order_cap < a.n) {
-                if (h->bvp_order_dev) CTR_CUDA(cudaFree(h->bvp_order_dev));
-                h->bvp_order_dev = nullptr;
-                h->bvp_order_cap = 0;
-                CTR_CUDA(cudaMalloc(&h->bvp_order_dev, (size_t)a.n * 5 + 1024 + 64));
-                h->bvp_order_cap = a.n;
-            }
-            int32_t* order = (int32_t*)h->bvp_order_dev;
-            int32_t* hist = order + h->bvp_order_cap;
-            uint8_t* key = (uint8_t*)(hist + 256);
-            CTR_CUDA(cudaMemsetAsync(hist, 0, 256 * sizeof(int32_t), st));
-            k_bvp_order_key<<<(int)((a.n + 255) / 256), 256, 0, st>>>(a, key, hist);
-            k_bvp_order_scan<<<1, 256, 0, st>>>(hist);
-            k_bvp_order_scatter<<<(int)((a.n + 255) / 256), 256, 0, st>>>(a.n, key, hist, order);
-            h->launches += 3;
+        {   // scheduling order (k_bvp_order_*): similar configurations together, long ones first
+            const int32_t* order = nullptr;
+            int rc = build_order(h, a.q, a.system, a.params, a.n, 0, st, &order);
+            if (rc) return rc;
             a.order = order;
         }
         const int per_block = (CTR_BLOCK / 32) * 10;     // 3 lanes per pass, 10 passes in flight per warp
@@ -2532,7 +2580,7 @@ int ctr_bvp_ik_dls(ctr_handle* h, const double* target_dev, double* q_dev, const
         CTR_CUDA(cudaMemsetAsync(active, 0, sizeof(int32_t), st));
         rc = bvp_launch(h, a, st);
         if (rc) return rc;
-        k_ik_dls_update<<<(int)((n + 255) / 256), 256, 0, st>>>(tips, target_dev, n, a.eps_q, lam, tol, q_dev, err_dev, iters_dev,
+        k_ik_dls_update<false><<<(int)((n + 255) / 256), 256, 0, st>>>(tips, target_dev, n, a.eps_q, lam, tol, q_dev, err_dev, iters_dev,
                                                                frozen, active);
         h->launches += 1;
         CTR_CUDA(cudaGetLastError());
