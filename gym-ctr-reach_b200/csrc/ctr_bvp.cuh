@@ -832,10 +832,41 @@ __global__ void k_bvp_order_key(const BvpArgs a, int many_first, uint8_t* __rest
             }
         }
         for (int k = 0; k < 3; ++k) beta[k] = a.q[(int64_t)k * a.n + i];
-        double S[9];
-        int pat[9];
-        int m = bvp_sections(L, Lc, beta, S, pat);
-        const double len = m > 0 ? S[m - 1] : 0.0, lmax = fmax(fmax(L[0], L[1]), L[2]);
+        // kept sections and deployed length (Segment.py:6-61) in registers: the 29-comparator network of build_sections, no table
+        double p[10], dtip[3];
+        p[0] = 0.0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            dtip[k] = __dadd_rn(L[k], beta[k]);
+            p[1 + k] = beta[k];
+            p[4 + k] = __dsub_rn(dtip[k], Lc[k]);
+            p[7 + k] = dtip[k];
+        }
+        const double bmin = dmin(dmin(beta[0], beta[1]), beta[2]);
+#define CS(x, y) cswap(p[x], p[y])
+        CS(0, 8); CS(1, 9); CS(2, 7); CS(3, 5); CS(4, 6);
+        CS(0, 2); CS(1, 4); CS(5, 8); CS(7, 9);
+        CS(0, 3); CS(2, 4); CS(5, 7); CS(6, 9);
+        CS(0, 1); CS(3, 6); CS(8, 9);
+        CS(1, 5); CS(2, 3); CS(4, 8); CS(6, 7);
+        CS(1, 2); CS(3, 5); CS(4, 6); CS(7, 8);
+        CS(2, 3); CS(4, 5); CS(6, 7);
+        CS(3, 4); CS(5, 6);
+#undef CS
+        double cum = 0.0, len = 0.0;
+        int m = 0;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+            const double ln = __dmul_rn(1e-5, floor(__dmul_rn(1e5, __dsub_rn(p[k + 1], p[k]))));
+            cum = __dadd_rn(cum, ln);
+            const double S = __dadd_rn(cum, bmin);
+            if (ln != 0.0 && S > 0.0) {
+                m += 1;
+                len = S;
+            }
+        }
+        if (!(bmin == bmin)) len = bmin;                                 // NaN joints: the key below sends them last
+        const double lmax = fmax(fmax(L[0], L[1]), L[2]);
         int lb = 15 - (int)(16.0 * len / lmax);                         // longer first
         lb = min(max(lb, 0), 15);
         m = min(max(m, 0), 15);
@@ -861,10 +892,24 @@ __global__ void k_bvp_order_scan(int32_t* __restrict__ hist) {          // one b
     }
     hist[t] = s[t] - hist[t];
 }
+// Scatter without hot global atomics (most configurations fall into a handful of bins): a block ranks its keys in shared memory, reserves one
+// range per bin with a single global atomic, and its threads write into the reserved ranges.
 __global__ void k_bvp_order_scatter(int64_t n, const uint8_t* __restrict__ key, int32_t* __restrict__ offs, int32_t* __restrict__ order) {
+    __shared__ int s_cnt[256];
+    __shared__ int s_base[256];
+    for (int k = threadIdx.x; k < 256; k += blockDim.x) s_cnt[k] = 0;
+    __syncthreads();
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    order[atomicAdd(&offs[key[i]], 1)] = (int32_t)i;
+    int kk = 0, rank = 0;
+    if (i < n) {
+        kk = key[i];
+        rank = atomicAdd(&s_cnt[kk], 1);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < 256; k += blockDim.x)
+        if (s_cnt[k]) s_base[k] = atomicAdd(&offs[k], s_cnt[k]);
+    __syncthreads();
+    if (i < n) order[s_base[kk] + rank] = (int32_t)i;
 }
 
 // Forward differences over the variant block: J f64 [18][n] (3 x 6 row-major), Cm f64 [9][n] (3 x 3), tip0 f64 [3][n]

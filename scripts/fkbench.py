@@ -28,6 +28,7 @@ seg = env.segment_tables(q)
 nsec = seg[3].double()
 length = (seg[1] * (torch.arange(9, device=q.device)[None, :] < seg[3][:, None])).max(dim=1).values
 print("given order            %.1f us (mean nfev %.1f)" % (timed(q), nfev.mean().item()))
-for name, key in (('nfev desc', -nfev), ('nsec desc', -nsec), ('nsec desc, length desc', -nsec * 10 - length), ('length desc', -length)):
+coarse = -nsec * 16 - torch.floor(16 * length / 0.431).clamp(0, 15) + torch.rand(n, device=q.device, dtype=torch.float64) * 0.5
+for name, key in (('coarse key, random ties', coarse), ('nfev desc', -nfev), ('nsec desc', -nsec), ('nsec desc, length desc', -nsec * 10 - length), ('length desc', -length)):
     print("%-22s %.1f us" % (name, timed(q[torch.argsort(key)].contiguous())))
 env.close()

@@ -514,6 +514,7 @@ def test_single_env_facade_random_rollout():
     """The reference's own test pattern (tests/unit_tests.py:40-58): random rollout through the gym id."""
     import ctr_reach_envs
     env = ctr_reach_envs.make('CTR-Reach-v0')
+    env.action_space.seed(11)                                           # reproducible: a test that draws from the OS entropy pool cannot be re-run
     try:
         for episode in range(3):
             ob = env.reset()
@@ -543,6 +544,7 @@ def test_single_env_facade_random_rollout():
 def test_single_env_facade_matches_oracle_episode(oracle_py):
     import ctr_reach_envs
     env = ctr_reach_envs.make('CTR-Reach-v0', evaluation=True)
+    env.action_space.seed(12)
     tc = oracle_py.derive_tube_constants(oracle_py.DEFAULT_SYSTEMS[0])
     low, high = oracle_py.joint_limits(tc['L'], False)
     try:
@@ -571,6 +573,7 @@ def test_facade_backbone_attributes_and_vec_get_attr(oracle_c, tube_constants, v
     import ctr_reach_envs
     from ctr_reach_envs.envs import CtrReachEnv
     env = CtrReachEnv(**ctr_reach_envs.default_kwargs())
+    env.action_space.seed(13)
     try:
         env.reset()
         env.step(env.action_space.sample())
@@ -582,7 +585,9 @@ def test_facade_backbone_attributes_and_vec_get_attr(oracle_c, tube_constants, v
             assert got.shape == want.shape and np.abs(got - want).max() < 1e-10
         live = env.render(mode='live')
         assert set(live) == {'t', 'achieved_goal', 'desired_goal', 'r1', 'r2', 'r3'} and live['t'] == 1
-        assert np.abs(live['r1'][-1] - live['achieved_goal']).max() < 1e-10           # tube 1 ends at the tip
+        # tube 1 ends at tip_pos[0], the FIRST sample within 1 mm of its tip (model.py:166-172): the tip itself unless the last section's
+        # samples are less than 1 mm apart (a last section under 29 mm) -- seen once in ~35 runs when this test drew unseeded actions
+        assert np.linalg.norm(live['r1'][-1] - live['achieved_goal']) < 1.1e-3
         assert env.render() is None
         tip = env.model.forward_kinematics(np.array([-0.1, -0.05, -0.02, 0.3, -0.2, 0.1]), 0)   # a direct call moves `r` with it
         assert np.abs(env.model.r[-1] - tip).max() < 1e-10
