@@ -129,7 +129,12 @@ int ctr_set_tube_params(ctr_handle *h, const double *params_dev, void *stream);
 
 /* Model.forward_kinematics (model.py:30-70).  joints f64 [6][n]; system i32 [n] or NULL (system 0);
  * params f64 [18][n] or NULL; outputs: tip f64 [3][n], R f64 [9][n] or NULL, info i32 [4][n] or NULL
- * (nfev, accepted steps, rejected steps, sections).  integrator/precision < 0 use the handle's config. */
+ * (nfev, accepted steps, rejected steps, sections).  integrator/precision < 0 use the handle's config.
+ * From 4096 configurations on, ctr_fk / ctr_fk_shape / ctr_jacobian / ctr_ik_dls (and the ctr_bvp_* calls) first build a hand-out
+ * order of the configurations in a buffer of the handle (counting sort on section count and deployed length: a lock-step warp costs
+ * its longest solve, so similar configurations are solved together).  It changes no result -- every output is addressed by
+ * configuration -- but such calls on ONE handle must not overlap on the GPU (one stream, or one handle per stream); the buffer is
+ * grown with cudaMalloc when a larger n arrives ($CTR_FK_SORT=0 switches the order off; ctr_jacobian_noalloc never uses it). */
 int ctr_fk(ctr_handle *h, const double *joints_dev, const int32_t *system_dev, const double *params_dev, int64_t n,
            int32_t integrator, int32_t precision, double *tip_dev, double *R_dev, int32_t *info_dev, void *stream);
 int ctr_fk_host(ctr_handle *h, const double *joints_host, const int32_t *system_host, int64_t n, int32_t integrator,
