@@ -561,7 +561,7 @@ def kernel_table(args, dev, pool, fma_peak, hbm_peak):
     sec = timed(fk)
     inf = info.double().sum(dim=1).tolist()                                # nfev, accepted, rejected, sections
     fk_flop = inf[0] * F_RHS + (inf[1] + inf[2]) * F_STEP + inf[3] * F_SECTION
-    fma_row("k_fk<f64,dp45>", sec, fk_flop, "131072 configs")
+    fma_row("k_fk<f64,dp45>", sec, fk_flop, "131072 configs, work-sorted hand-out order (pre-pass included)")
     # ---- k_fk_shape: the same solves + 30 dense-output samples per section
     shape = torch.empty((N, 270, 3), dtype=torch.float64, device=dev)
     npts = torch.empty(N, dtype=torch.int32, device=dev)
@@ -621,7 +621,7 @@ def kernel_table(args, dev, pool, fma_peak, hbm_peak):
     # algorithmic flops: RK23 = 3 RHS per attempt (+2 per section start), RHS of the 20-state model ~ 330 flop (6 sincos, the
     # two curvature sums of CTR_Model.py:84-112, R u_hat), + 20 x 12 for the stage combinations and the error norm
     fma_row("k_bvp_pass_g (RK23, 20 states)", sec, steps_b * (3 * 330.0 + 240.0),
-            "%d configs, %.0f accepted steps each; 3 lanes per pass, state in registers, groups refill themselves from a work counter" % (nb, steps_b / nb))
+            "%d configs, %.0f accepted steps each; 3 lanes per pass, state in registers, groups refill themselves from a work counter, sorted hand-out order" % (nb, steps_b / nb))
     sec = timed(lambda: e.bvp_jacobian(qb[:32768], compliance=False), reps=3, warm=1)
     fma_row("ctr_bvp_jacobian (7 passes)", sec, 7.0 * steps_b / nb * 32768 * (3 * 330.0 + 240.0), "32768 configs = 229376 passes")
     e.close()
