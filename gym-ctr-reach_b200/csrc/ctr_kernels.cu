@@ -1035,7 +1035,7 @@ struct ctr_handle {
     unsigned bvp_launches;
     void* bvp_order_dev;       // scheduling order of k_bvp_pass_g: order i32 [cap] | hist i32 [256] | key u8 [cap]
     int64_t bvp_order_cap;
-    int bvp_sort;              // order the configurations before a k_bvp_pass_g / k_fk / k_fk_shape launch ($CTR_BVP_SORT or $CTR_FK_SORT, default 1; from 4096 configurations on)
+    int bvp_sort;              // order the configurations before a large k_bvp_pass_g / k_fk / k_fk_shape launch ($CTR_BVP_SORT or $CTR_FK_SORT, default 1)
     int64_t ik_cap;            // ctr_jacobian / ctr_ik_dls scratch: joints f64 [6][7n] | tips f64 [3][7n] | system i32 [7n] | frozen u8 [n] | active i32
     void* ik_dev;
 };
@@ -1465,7 +1465,10 @@ int ctr_set_tube_params(ctr_handle* h, const double* params_dev, void* stream) {
 // Work-sorted hand-out order of n configurations (k_bvp_order_* in ctr_bvp.cuh: counting sort on section count and deployed length)
 // in the handle's order buffer; *order = null below 4096 configurations or with $CTR_FK_SORT=0 / $CTR_BVP_SORT=0.
 static int build_order(ctr_handle* h, const double* q_dev, const int32_t* system_dev, const double* params_dev, int64_t n,
-                       int many_first, cudaStream_t st, const int32_t** order_out);
+                       int many_first, int64_t min_n, cudaStream_t st, const int32_t** order_out);
+// the pre-pass costs ~20 us (a memset and three small launches): it pays from ~65536 env-path solves (k_fk: 3 ns each, 10 % gained)
+// and from ~16384 BVP passes (14 ns each, 19 % gained) on
+constexpr int64_t ORDER_MIN_FK_SOLVES = 65536, ORDER_MIN_BVP_PASSES = 16384;
 
 // columns = n_cols joint columns; order (or null) permutes groups of `group` consecutive columns
 static int fk_launch(ctr_handle* h, const double* joints_dev, const int32_t* system_dev, const double* params_dev, int64_t n,
@@ -1490,7 +1493,7 @@ int ctr_fk(ctr_handle* h, const double* joints_dev, const int32_t* system_dev, c
     cudaStream_t st = (cudaStream_t)stream;
     // a lock-step warp costs its longest solve: hand the configurations out sorted by what their section tables say about their length
     const int32_t* order = nullptr;
-    int rc = build_order(h, joints_dev, system_dev, params_dev, n, 1, st, &order);
+    int rc = build_order(h, joints_dev, system_dev, params_dev, n, 1, ORDER_MIN_FK_SOLVES, st, &order);
     if (rc) return rc;
     return fk_launch(h, joints_dev, system_dev, params_dev, n, integrator, precision, tip_dev, R_dev, info_dev, st, order, 1);
 }
@@ -2208,7 +2211,7 @@ int ctr_fk_shape(ctr_handle* h, const double* joints_dev, const int32_t* system_
     CTR_CUDA(cudaSetDevice(h->device));
     const int32_t* order = nullptr;              // work-sorted hand-out order, as for ctr_fk
     {
-        int rc = build_order(h, joints_dev, system_dev, params_dev, n, 1, (cudaStream_t)stream, &order);
+        int rc = build_order(h, joints_dev, system_dev, params_dev, n, 1, ORDER_MIN_FK_SOLVES / 2, (cudaStream_t)stream, &order);
         if (rc) return rc;
     }
     if (h->all_uy_zero && !params_dev)
@@ -2255,7 +2258,7 @@ static int ik_solve7(ctr_handle* h, const IkScratch& sc, const double* q_dev, co
     h->launches += 1;
     CTR_CUDA(cudaGetLastError());
     const int32_t* order = nullptr;              // configurations in work-sorted order, the 7 columns of each one together
-    int rc = sorted ? build_order(h, q_dev, system_dev, nullptr, n, 1, st, &order) : 0;   // (the order buffer is a cudaMalloc: not for ctr_jacobian_noalloc)
+    int rc = sorted ? build_order(h, q_dev, system_dev, nullptr, n, 1, (ORDER_MIN_FK_SOLVES + 6) / 7, st, &order) : 0;   // (the order buffer is a cudaMalloc: not for ctr_jacobian_noalloc)
     if (rc) return rc;
     return fk_launch(h, sc.block, system_dev ? sc.system : nullptr, nullptr, 7 * n, CTR_INTEGRATOR_DP45, CTR_PRECISION_F64, sc.tips,
                      nullptr, nullptr, st, order, 7);
@@ -2411,9 +2414,9 @@ static BvpArgs bvp_args(ctr_handle* h, const double* q, const double* f, const d
     return a;
 }
 static int build_order(ctr_handle* h, const double* q_dev, const int32_t* system_dev, const double* params_dev, int64_t n,
-                       int many_first, cudaStream_t st, const int32_t** order_out) {
+                       int many_first, int64_t min_n, cudaStream_t st, const int32_t** order_out) {
     *order_out = nullptr;
-    if (!h->bvp_sort || n < 4096 || n >= (int64_t)1 << 31) return 0;
+    if (!h->bvp_sort || n < min_n || n >= (int64_t)1 << 31) return 0;
     if (h->bvp_order_cap < n) {
         if (h->bvp_order_dev) CTR_CUDA(cudaFree(h->bvp_order_dev));
         h->bvp_order_dev = nullptr;
@@ -2455,7 +2458,7 @@ static int bvp_launch(ctr_handle* h, const BvpArgs& a_in, cudaStream_t st) {
         CTR_CUDA(cudaMemsetAsync(a.next, 0, sizeof(unsigned long long), st));
         {   // scheduling order (k_bvp_order_*): similar configurations together, long ones first
             const int32_t* order = nullptr;
-            int rc = build_order(h, a.q, a.system, a.params, a.n, 0, st, &order);
+            int rc = build_order(h, a.q, a.system, a.params, a.n, 0, (ORDER_MIN_BVP_PASSES + bvp_variants(a.mode) - 1) / bvp_variants(a.mode), st, &order);
             if (rc) return rc;
             a.order = order;
         }

@@ -130,10 +130,12 @@ int ctr_set_tube_params(ctr_handle *h, const double *params_dev, void *stream);
 /* Model.forward_kinematics (model.py:30-70).  joints f64 [6][n]; system i32 [n] or NULL (system 0);
  * params f64 [18][n] or NULL; outputs: tip f64 [3][n], R f64 [9][n] or NULL, info i32 [4][n] or NULL
  * (nfev, accepted steps, rejected steps, sections).  integrator/precision < 0 use the handle's config.
- * From 4096 configurations on, ctr_fk / ctr_fk_shape / ctr_jacobian / ctr_ik_dls (and the ctr_bvp_* calls) first build a hand-out
+ * Large launches (ctr_fk from 65536 solves, ctr_fk_shape from 32768, ctr_jacobian / ctr_ik_dls from 9363 configurations, the ctr_bvp_*
+ * calls from 16384 passes) first build a hand-out
  * order of the configurations in a buffer of the handle (counting sort on section count and deployed length: a lock-step warp costs
  * its longest solve, so similar configurations are solved together).  It changes no result -- every output is addressed by
- * configuration -- but such calls on ONE handle must not overlap on the GPU (one stream, or one handle per stream); the buffer is
+ * configuration; the one neighbour effect of the env-path kernels exists in any order: a warp that holds a solve with NaN or
+ * |angle difference| >= 9e4 rad runs the library sincos for all its 10 solves, 1 ulp from the polynomial one -- but such calls on ONE handle must not overlap on the GPU (one stream, or one handle per stream); the buffer is
  * grown with cudaMalloc when a larger n arrives ($CTR_FK_SORT=0 switches the order off; ctr_jacobian_noalloc never uses it). */
 int ctr_fk(ctr_handle *h, const double *joints_dev, const int32_t *system_dev, const double *params_dev, int64_t n,
            int32_t integrator, int32_t precision, double *tip_dev, double *R_dev, int32_t *info_dev, void *stream);
@@ -297,7 +299,7 @@ int ctr_jacobian_noalloc(ctr_handle *h, const double *joints_dev, const int32_t 
  * ctr_bvp_ik_dls    = src/jacobian_controller.py:19-53 on this model: q [6][n] in/out, target [3][n]; as ctr_ik_dls.  Synchronises.
  * Streams: ctr_bvp_jacobian / _solve / _ik_dls keep their intermediate results in ONE scratch buffer of the handle (grown with
  * cudaMalloc on demand): calls on the same handle must not overlap on the GPU (one stream, or one handle per stream).  The same
- * holds for ctr_bvp_pass from 4096 configurations on (its scheduling order -- which configuration a free lane group takes next; it
+ * holds for ctr_bvp_pass from 16384 passes on (its scheduling order -- which configuration a free lane group takes next; it
  * does not change any result -- is built in a buffer of the handle); below that it keeps no state but a pass counter taken from a
  * ring of 64, so up to 64 such launches may be in flight at once. */
 int ctr_bvp_pass(ctr_handle *h, const double *q_dev, const double *f_dev, const double *u_dev, const int32_t *system_dev,

@@ -212,16 +212,16 @@ def test_bvp_argument_errors_and_joint_box_ends(oracle_c, oracle_py, vec_factory
 
 @pytest.mark.gpu
 def test_bvp_scheduling_order_does_not_change_results(oracle_c, oracle_py, vec_factory, monkeypatch):
-    """From 4096 configurations on, the passes are handed out in a sorted order (few sections first, long robots first;
+    """From 16384 passes on, the passes are handed out in a sorted order (few sections first, long robots first;
     k_bvp_order_*).  Same inputs with the ordering switched off ($CTR_BVP_SORT=0, read at ctr_create): bit-identical outputs,
     failed rows (NaN joints) included; Jacobian variants too."""
     rng = np.random.RandomState(21)
-    n = 6000
+    n = 18000
     systems = np.stack([oracle_py.randomize_system(rng, oracle_py.DEFAULT_SYSTEMS[rng.randint(4)], 0.05) for _ in range(n)])
     P = oracle_c.derive(systems)
     q = np.stack([oracle_py.sample_goal(rng, P[i, :3]) for i in range(n)]).astype(np.float64)
     f = rng.uniform(-0.3, 0.3, size=(n, 3))
-    q[[17, 4100, 5999], 1] = np.nan
+    q[[17, 4100, 17999], 1] = np.nan
     monkeypatch.setenv('CTR_BVP_SORT', '1')
     env_sorted = vec_factory(16)
     monkeypatch.setenv('CTR_BVP_SORT', '0')
@@ -232,7 +232,7 @@ def test_bvp_scheduling_order_does_not_change_results(oracle_c, oracle_py, vec_f
         assert np.array_equal(a[k].cpu().numpy(), b[k].cpu().numpy(), equal_nan=True), k
     assert (a['steps'].cpu().numpy() == -1).sum() == 3
     ok = np.ones(n, dtype=bool)
-    ok[[17, 4100, 5999]] = False
+    ok[[17, 4100, 17999]] = False
     Ja, Ca, ta = env_sorted.bvp_jacobian(q[ok][:4500], force=f[ok][:4500], params=P[ok][:4500])
     Jb, Cb, tb = env_plain.bvp_jacobian(q[ok][:4500], force=f[ok][:4500], params=P[ok][:4500])
     assert np.array_equal(Ja.cpu().numpy(), Jb.cpu().numpy()) and np.array_equal(Ca.cpu().numpy(), Cb.cpu().numpy())

@@ -318,3 +318,34 @@ def test_checkpoint_restore_reproduces_the_run(vec_factory, extra):
     small = vec_factory(n // 2, **kw)
     with pytest.raises(Exception):
         small.restore(blob)
+
+
+@pytest.mark.gpu
+def test_work_sorted_hand_out_order_does_not_change_results(vec_factory, monkeypatch):
+    """Large one-shot launches (ctr_fk from 65536 solves, ctr_fk_shape from 32768, ctr_jacobian from 9363 configurations) are
+    solved in a work-sorted order built by a counting-sort pre-pass (build_order).  Same inputs on a handle with the order
+    switched off ($CTR_FK_SORT=0, read at ctr_create): every output bit-identical, four systems mixed.  (Finite joints: a warp that
+    holds a solve with NaN or |angle difference| >= 9e4 rad runs the library sincos for all its 10 solves, 1 ulp away from the polynomial
+    one, so next to such a row the last bits depend on which rows share its warp -- in any order.)"""
+    import torch
+    n = 70000
+    monkeypatch.setenv('CTR_FK_SORT', '1')
+    a = vec_factory(n, select_systems=[0, 1, 2, 3], seed=9)
+    monkeypatch.setenv('CTR_FK_SORT', '0')
+    b = vec_factory(16, select_systems=[0, 1, 2, 3])
+    a.reset()
+    q = a.buffer('joints').t().to(torch.float64).contiguous()
+    sysid = a.buffer('system').clone()
+    ta, Ra, ia = a.forward_kinematics(q, system=sysid, return_info=True)
+    tb, Rb, ib = b.forward_kinematics(q, system=sysid, return_info=True)
+    assert torch.equal(ia, ib) and torch.equal(torch.nan_to_num(ta, nan=7.0), torch.nan_to_num(tb, nan=7.0))
+    assert torch.equal(torch.nan_to_num(Ra, nan=7.0), torch.nan_to_num(Rb, nan=7.0))
+    qs, ss = q[1000:41000].contiguous(), sysid[1000:41000].contiguous()
+    sa, sb = a.backbone_shape(qs, system=ss), b.backbone_shape(qs, system=ss)
+    assert torch.equal(sa[1], sb[1]) and torch.equal(sa[2], sb[2]) and torch.equal(sa[3], sb[3])
+    mask = (torch.arange(270, device=qs.device)[None, :] < sa[1][:, None])[:, :, None]
+    assert torch.equal(sa[0] * mask, sb[0] * mask)                      # rows past npts are unspecified
+    qj, sj = q[50000:60000].contiguous(), sysid[50000:60000].contiguous()
+    Ja, tja = a.jacobian(qj, system=sj)
+    Jb, tjb = b.jacobian(qj, system=sj)
+    assert torch.equal(Ja, Jb) and torch.equal(tja, tjb)
