@@ -41,14 +41,17 @@ if os.environ.get('FK_NEXT'):
     gen = torch.Generator(device=q.device); gen.manual_seed(3)
     for _ in range(5):
         env.step(((torch.rand((n, 6), device=q.device, generator=gen) * 2 - 1) * lim).contiguous())
+    qm = env.buffer('joints').t().to(torch.float64).contiguous()
+    nfevm = env.forward_kinematics(qm, return_info=True)[2][:, 0].double()
+    env.step(((torch.rand((n, 6), device=q.device, generator=gen) * 2 - 1) * lim).contiguous())
     q0 = env.buffer('joints').t().to(torch.float64).contiguous()
     nfev0 = env.forward_kinematics(q0, return_info=True)[2][:, 0].double()
     env.step(((torch.rand((n, 6), device=q.device, generator=gen) * 2 - 1) * lim).contiguous())
     q1 = env.buffer('joints').t().to(torch.float64).contiguous()
     keep = (env.buffer('t') > 0)                       # envs that were not reset by this step
-    q0, q1, nfev0 = q0[keep], q1[keep], nfev0[keep]
+    q0, q1, nfev0, nfevm = q0[keep], q1[keep], nfev0[keep], nfevm[keep]
     m = (q1.shape[0] // 640) * 640
-    q0, q1, nfev0 = q0[:m], q1[:m].contiguous(), nfev0[:m]
+    q0, q1, nfev0, nfevm = q0[:m], q1[:m].contiguous(), nfev0[:m], nfevm[:m]
     nfev1 = env.forward_kinematics(q1, return_info=True)[2][:, 0].double()
     seg1 = env.segment_tables(q1)
     nsec1 = seg1[3].double()
@@ -60,6 +63,7 @@ if os.environ.get('FK_NEXT'):
         return q1[idx.view(-1)].contiguous()
     import os as _os
     for name, key in (("unsorted", None), ("last step's nfev (k_step's key), windows of 640", -nfev0), ("this step's nfev (ceiling), windows of 640", -nfev1),
+                      ("mean of the last two steps' nfev", -(nfev0 + nfevm)), ("0.75 last + 0.25 the one before", -(3 * nfev0 + nfevm)),
                       ("last nfev + 12 x section-count change", -(nfev0 + 12 * (nsec1 - nsec0))), ("this step's (nsec, length)", -nsec1 * 10 - len1)):
         qq = q1 if key is None else windowed(key)
         print("    %-52s %.1f us" % (name, timed(qq)))
